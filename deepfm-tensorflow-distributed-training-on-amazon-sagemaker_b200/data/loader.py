@@ -1,0 +1,101 @@
+"""Batch loader: native producer threads -> ring of pinned host buffers.
+
+The reference's ``input_fn`` (HVD.py:104-161) is
+``TFRecordDataset -> shard -> batch(drop_remainder=True) -> parse_example -> repeat -> prefetch``.
+``BatchLoader`` is that pipeline as a C++ thread pool (csrc/io/loader.cc) that decodes
+straight into page-locked torch tensors, so the trainer can issue one async H2D copy
+per tensor with no intermediate staging.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Iterator, List, Optional, Sequence
+
+import torch
+
+from .. import _native
+from .tfrecord import DataError, _lib
+
+
+class _Cfg(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "field_size", "batch_size", "num_epochs", "drop_remainder", "shard_n", "shard_i", "num_workers",
+        "num_slots", "ids_i32", "verify_crc", "streaming", "reserved")]
+
+
+@dataclass
+class HostBatch:
+    """Views into one ring slot; valid until the next batch is requested."""
+    feat_ids: torch.Tensor   # [n, F] int32|int64, pinned when CUDA is present
+    feat_vals: torch.Tensor  # [n, F] float32
+    labels: torch.Tensor     # [n]    float32
+    count: int
+
+
+class BatchLoader:
+    def __init__(self, paths: Sequence[str], field_size: int, batch_size: int, num_epochs: int = 1,
+                 drop_remainder: bool = True, shard_n: int = 1, shard_i: int = 0, num_workers: int = 4,
+                 num_slots: int = 4, ids_dtype: torch.dtype = torch.int32, verify_crc: bool = True,
+                 streaming: bool = False, pin_memory: Optional[bool] = None):
+        lib = _lib()
+        if not getattr(lib, "_loader_typed", False):
+            lib.dfio_loader_create.restype = C.c_void_p
+            lib.dfio_loader_create.argtypes = [C.POINTER(_Cfg), C.POINTER(C.c_char_p), C.c_int,
+                                               C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+            lib.dfio_loader_next.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+            lib.dfio_loader_release.argtypes = [C.c_void_p, C.c_int]
+            lib.dfio_loader_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+            lib.dfio_loader_destroy.argtypes = [C.c_void_p]
+            lib._loader_typed = True
+        self._lib = lib
+        assert ids_dtype in (torch.int32, torch.int64)
+        if pin_memory is None:
+            pin_memory = torch.cuda.is_available()
+        self.field_size, self.batch_size = field_size, batch_size
+        self._ids = [torch.empty((batch_size, field_size), dtype=ids_dtype, pin_memory=pin_memory) for _ in range(num_slots)]
+        self._vals = [torch.empty((batch_size, field_size), dtype=torch.float32, pin_memory=pin_memory) for _ in range(num_slots)]
+        self._labels = [torch.empty((batch_size,), dtype=torch.float32, pin_memory=pin_memory) for _ in range(num_slots)]
+        cfg = _Cfg(field_size, batch_size, max(1, num_epochs), int(drop_remainder), max(1, shard_n), shard_i,
+                   num_workers, num_slots, int(ids_dtype == torch.int32), int(verify_crc), int(streaming), 0)
+        arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
+        vp = lambda ts: (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+        self._h = lib.dfio_loader_create(C.byref(cfg), arr, len(paths), vp(self._ids), vp(self._vals), vp(self._labels))
+        if not self._h:
+            raise DataError(lib.dfio_last_error().decode())
+        self._held: Optional[int] = None
+
+    def __iter__(self) -> Iterator[HostBatch]:
+        return self
+
+    def __next__(self) -> HostBatch:
+        if self._h is None:
+            raise StopIteration
+        if self._held is not None:
+            self._lib.dfio_loader_release(self._h, self._held)
+            self._held = None
+        slot, count = C.c_int(), C.c_int()
+        r = self._lib.dfio_loader_next(self._h, C.byref(slot), C.byref(count))
+        if r == 0:
+            raise StopIteration
+        if r < 0:
+            raise DataError(self._lib.dfio_last_error().decode())
+        s, n = slot.value, count.value
+        self._held = s
+        return HostBatch(self._ids[s][:n], self._vals[s][:n], self._labels[s][:n], n)
+
+    def stats(self):
+        r, b, y = C.c_int64(), C.c_int64(), C.c_int64()
+        self._lib.dfio_loader_stats(self._h, C.byref(r), C.byref(b), C.byref(y))
+        return {"records": r.value, "batches": b.value, "bytes": y.value}
+
+    def close(self) -> None:
+        if self._h is not None:
+            h, self._h = self._h, None
+            self._lib.dfio_loader_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
