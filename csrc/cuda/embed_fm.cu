@@ -1,0 +1,141 @@
+// deepfm_embed_fm_fwd: one pass over the batch that replaces the reference's
+//   embedding_lookup(fm_w) * x, reduce_sum                      (HVD.py:196-198)
+//   embedding_lookup(fm_v) * x, (sum e)^2, sum e^2, 0.5*sum     (HVD.py:200-206)
+//   reshape to [B, F*K]                                         (HVD.py:219-221)
+// and, when training, also starts the sparse-gradient bookkeeping: every distinct id of
+// the batch claims a compact "slot" (slot_of[id]) and is appended to uniq_ids, so the
+// backward pass can reduce row gradients into a dense [n_unique, K] buffer and the
+// optimizer touches each table row exactly once (lazy update; dedupe that TF's
+// IndexedSlices path never did).
+//
+// One warp per example; lane k owns embedding component(s) k, k+32, ...
+// Outputs: e (bf16, MLP input, row pitch `pitch`), s_sum [B,K] fp32 = sum_f e,
+//          fm_part [B] = fm_bias + y_w + y_v.
+#include "engine.cuh"
+
+namespace dfm {
+
+constexpr int kEmbedWarps = 8;
+constexpr int kMaxKPerLane = 4;   // embedding_size <= 128
+
+template <int KPL>   // embedding components per lane: embedding_size <= 32*KPL
+__global__ void __launch_bounds__(kEmbedWarps * 32)
+embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
+                    const float* __restrict__ fm_w, const float* __restrict__ fm_v,
+                    const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
+                    float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
+                    StepState* __restrict__ st, int* __restrict__ slot_of, int* __restrict__ uniq_ids,
+                    int dedupe) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * kEmbedWarps + warp;
+  const int count = st->count;
+  if (blockIdx.x == 0 && threadIdx.x == 0) st->loss_sum = 0.f;   // consumed by mlp_fwd of this step
+  if (b >= count) return;
+
+  const int* my_ids = ids + size_t(b) * F;
+  const float* my_vals = vals + size_t(b) * F;
+
+  float S[KPL], Q[KPL];
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) S[j] = Q[j] = 0.f;
+  float yw = 0.f;
+
+  for (int f0 = 0; f0 < F; f0 += 32) {
+    const int nf = min(32, F - f0);
+    int id_l = 0;
+    float x_l = 0.f;
+    if (lane < nf) {
+      id_l = __ldg(my_ids + f0 + lane);
+      x_l = __ldg(my_vals + f0 + lane);
+      yw += __ldg(fm_w + id_l) * x_l;
+      if (dedupe) {
+        // claim a slot for this id if nobody has yet (-1 free, -2 being claimed, >=0 slot)
+        if (slot_of[id_l] == -1 && atomicCAS(&slot_of[id_l], -1, -2) == -1) {
+          const int s = atomicAdd(&st->n_unique, 1);
+          uniq_ids[s] = id_l;
+          slot_of[id_l] = s;
+        }
+      }
+    }
+    // 4 fields in flight per iteration: independent 128 B row gathers
+    for (int f = 0; f < nf; f += 4) {
+      float row[4][KPL];
+      float xs[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int ff = min(f + u, nf - 1);
+        const int id = __shfl_sync(0xffffffffu, id_l, ff);
+        xs[u] = __shfl_sync(0xffffffffu, x_l, ff);
+        const float* src = fm_v + size_t(id) * Ke;
+#pragma unroll
+        for (int j = 0; j < KPL; ++j) {
+          const int k = lane + 32 * j;
+          row[u][j] = k < Ke ? __ldg(src + k) : 0.f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (f + u < nf) {
+          __nv_bfloat16* dst = e + size_t(b) * pitch + size_t(f0 + f + u) * Ke;
+#pragma unroll
+          for (int j = 0; j < KPL; ++j) {
+            const int k = lane + 32 * j;
+            if (k < Ke) {
+              const float ev = row[u][j] * xs[u];
+              S[j] += ev;
+              Q[j] += ev * ev;
+              dst[k] = __float2bfloat16(ev);
+            }
+          }
+        }
+      }
+    }
+  }
+
+  float yv = 0.f;
+#pragma unroll
+  for (int j = 0; j < KPL; ++j) {
+    const int k = lane + 32 * j;
+    if (k < Ke) {
+      yv += S[j] * S[j] - Q[j];
+      s_sum[size_t(b) * Ke + k] = S[j];
+    }
+  }
+  float tot = yw + 0.5f * yv;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+  if (lane == 0) fm_part[b] = tot + __ldg(fm_bias);
+}
+
+// Writes the constant ones column (and zeroes the pad) of an activation buffer.
+__global__ void fill_ones_column_kernel(__nv_bfloat16* act, int rows, int pitch, int k_valid) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  for (int c = k_valid; c < pitch; ++c) act[size_t(r) * pitch + c] = __float2bfloat16(c == k_valid ? 1.f : 0.f);
+}
+
+int launch_embed_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v,
+                        const float* fm_bias, __nv_bfloat16* e, int pitch, float* s_sum, float* fm_part,
+                        int F, int Ke, int batch_max, StepState* st, int* slot_of, int* uniq_ids,
+                        int dedupe, cudaStream_t stream) {
+  DFM_REQUIRE(Ke <= 32 * kMaxKPerLane, "embedding_size %d > %d is not supported", Ke, 32 * kMaxKPerLane);
+  const int grid = ceil_div(batch_max, kEmbedWarps);
+#define DFM_EMBED_LAUNCH(KPL)                                                                          \
+  embed_fm_fwd_kernel<KPL><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, \
+                                                                  s_sum, fm_part, F, Ke, st, slot_of,   \
+                                                                  uniq_ids, dedupe)
+  if (Ke <= 32) DFM_EMBED_LAUNCH(1);
+  else if (Ke <= 64) DFM_EMBED_LAUNCH(2);
+  else DFM_EMBED_LAUNCH(4);
+#undef DFM_EMBED_LAUNCH
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+int launch_fill_ones_column(__nv_bfloat16* act, int rows, int pitch, int k_valid, cudaStream_t stream) {
+  fill_ones_column_kernel<<<ceil_div(rows, 256), 256, 0, stream>>>(act, rows, pitch, k_valid);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+}  // namespace dfm

@@ -1,0 +1,211 @@
+// Shared definitions of the DeepFM step engine: the device-side state block, the
+// per-step buffer table, and the launch prototypes of the fused kernels.
+//
+// Layout conventions (all row-major):
+//   K[0] = field_size * embedding_size, N[l] = deep_layers[l], K[l+1] = N[l]
+//   act[l]  bf16 [B, pitch[l]]  input of layer l (act[0] = e = v[id]*x), pitch[l] = round_up(K[l]+1, 8);
+//           column K[l] is a constant 1.0 so that the weight-gradient GEMM also yields the bias row
+//   dz[l]   bf16 [B, N[l]]      gradient w.r.t. the pre-activation of layer l
+//   dz[L]   bf16 [B, 16]        column 0 = dlogit (out layer has one output; padded to a legal UMMA N)
+//   P[l]    fp32 [K[l]+1, N[l]] weights with the bias as last row (l = L: out layer, N = 1)
+//   Wb[l]   bf16 copy of P[l] (same shape) used as the tensor-core operand
+#pragma once
+
+#include "common.cuh"
+
+namespace dfm {
+
+constexpr int kMaxLayers = 6;       // hidden layers
+constexpr int kTileM = 128;         // batch rows per CTA
+constexpr int kChunkK = 64;         // K elements per pipeline stage (128 B of bf16)
+
+// Scalars that change every step live in device memory so a captured CUDA graph can be
+// replayed without re-recording kernel arguments.
+struct StepState {
+  int count;          // valid rows of the current batch
+  int step;           // optimizer step number, 1-based (TF global_step + 1)
+  float lr;           // learning rate (already multiplied by world size, HVD.py:171)
+  float loss_sum;     // sum of per-example BCE over the batch (this rank)
+  int n_unique;       // distinct table rows touched by the current batch
+  int sparse_done;    // CTAs of the sparse-apply kernel that have finished (last one resets)
+  int train;          // 1: dropout active, gradients produced
+  int pad;
+};
+
+struct OptHyper {
+  int kind;            // DFM_OPT_*
+  float beta1, beta2, eps;       // Adam
+  float momentum;                // Momentum
+  float ftrl_lr_power, ftrl_l1, ftrl_l2;
+  float l2_reg;                  // applied to fm_w / fm_v only (HVD.py:266-267)
+};
+
+struct MlpShape {
+  int L;                       // hidden layers
+  int K[kMaxLayers + 1];       // K[l] input width of layer l (l = L: out layer)
+  int N[kMaxLayers + 1];       // N[l] output width (N[L] = 1)
+  int pitch[kMaxLayers + 1];   // act[l] row pitch in elements
+  float keep[kMaxLayers];      // dropout keep probability after layer l (1 = off)
+};
+
+// -------- one uniform apply rule for all five optimizers (TF1 formulas) ----------
+//   Adam      m,v slots;   lr_t = lr*sqrt(1-b2^t)/(1-b1^t); p -= lr_t*m/(sqrt(v)+eps)      HVD.py:282-284
+//   Adagrad   acc slot (init 1e-8); p -= lr*g/sqrt(acc)                                     HVD.py:286-288
+//   Momentum  acc = mom*acc + g; p -= lr*acc                                                HVD.py:290-292
+//   Ftrl      accum (init 0.1), linear; TF FtrlOptimizer defaults                            HVD.py:294
+//   GD        p -= lr*g
+struct OptStepConsts {
+  float lr, lr_t, b1, b2, eps, mom, lr_power, l1, l2;
+  int kind;
+};
+
+__device__ __forceinline__ OptStepConsts make_opt_consts(const OptHyper& h, float lr, int step) {
+  OptStepConsts c;
+  c.kind = h.kind; c.lr = lr; c.b1 = h.beta1; c.b2 = h.beta2; c.eps = h.eps; c.mom = h.momentum;
+  c.lr_power = h.ftrl_lr_power; c.l1 = h.ftrl_l1; c.l2 = h.ftrl_l2;
+  c.lr_t = lr;
+  if (h.kind == DFM_OPT_ADAM) {
+    const float t = static_cast<float>(step);
+    c.lr_t = lr * sqrtf(1.f - powf(h.beta2, t)) / (1.f - powf(h.beta1, t));
+  }
+  return c;
+}
+
+__device__ __forceinline__ void opt_apply(const OptStepConsts& c, float g, float& p, float& s0, float& s1) {
+  switch (c.kind) {
+    case DFM_OPT_ADAM: {
+      s0 = c.b1 * s0 + (1.f - c.b1) * g;
+      s1 = c.b2 * s1 + (1.f - c.b2) * g * g;
+      p -= c.lr_t * s0 / (sqrtf(s1) + c.eps);
+    } break;
+    case DFM_OPT_ADAGRAD: {
+      s0 += g * g;
+      p -= c.lr * g * rsqrtf(s0);
+    } break;
+    case DFM_OPT_MOMENTUM: {
+      s0 = c.mom * s0 + g;
+      p -= c.lr * s0;
+    } break;
+    case DFM_OPT_FTRL: {
+      // s0 = accum, s1 = linear
+      const float acc_new = s0 + g * g;
+      float sigma, quad;
+      if (c.lr_power == -0.5f) {
+        sigma = (sqrtf(acc_new) - sqrtf(s0)) / c.lr;
+        quad = sqrtf(acc_new) / c.lr + 2.f * c.l2;
+      } else {
+        sigma = (powf(acc_new, -c.lr_power) - powf(s0, -c.lr_power)) / c.lr;
+        quad = powf(acc_new, -c.lr_power) / c.lr + 2.f * c.l2;
+      }
+      s1 += g - sigma * p;
+      const float lin = s1;
+      p = fabsf(lin) > c.l1 ? (copysignf(c.l1, lin) - lin) / quad : 0.f;
+      s0 = acc_new;
+    } break;
+    default: {  // GD
+      p -= c.lr * g;
+    } break;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Kernel parameter blocks (passed as __grid_constant__) and launchers
+// ---------------------------------------------------------------------------
+struct FwdMaps {
+  CUtensorMap e;                  // act[0] as [B, K0], box {64, 128}
+  CUtensorMap w[kMaxLayers];      // Wb[l] as [K_l, N_l] (N contiguous), box {64, 64}
+};
+
+struct FwdParams {
+  MlpShape sh;
+  const float* P[kMaxLayers + 1];        // fp32 masters (bias rows, out layer)
+  __nv_bfloat16* act[kMaxLayers + 1];    // act[l+1] is written here
+  const float* fm_part;
+  const float* labels;                   // may be null (pure inference)
+  float* logit;
+  float* prob;
+  float* dlogit;
+  StepState* st;
+  unsigned long long seed;
+  int stages;
+  int b_slot_bytes;
+  int a_region_chunks;
+};
+
+struct BwdMaps {
+  CUtensorMap w[kMaxLayers];   // Wb[l] as [K_l rows, N_l cols], box {64, min(256, K_l)}  (K-major B)
+  CUtensorMap dz0;             // dz[0] as [B, N_0], box {64, 128}                         (K-major A)
+};
+
+struct BwdParams {
+  MlpShape sh;
+  const __nv_bfloat16* act[kMaxLayers + 1];
+  __nv_bfloat16* dz[kMaxLayers + 1];
+  const float* w_out;          // P[L]
+  const float* dlogit;
+  StepState* st;
+  int stages;
+  int b_slot_bytes;
+  int a_region_chunks;
+  // embed_bwd only
+  const int* ids;
+  const float* vals;
+  const float* s_sum;
+  const int* slot_of;
+  float* G;                    // [slots, Ke]
+  float* Gw;                   // [slots]
+  int F, Ke;
+};
+
+struct WgradItem {
+  int layer;      // 0..L (L = out layer)
+  int m0;         // first row of dP_l handled by this CTA (multiple of 128)
+  int n0;         // first column (multiple of 256)
+  int n_here;     // columns (multiple of 16, <= 256)
+  int k_begin;    // batch range [k_begin, k_end), multiples of 64
+  int k_end;
+};
+
+struct WgradMaps {
+  CUtensorMap act[kMaxLayers + 1];   // [B, K_l+1], box {64, 64}
+  CUtensorMap dz[kMaxLayers + 1];    // [B, N_l],   box {64, 64}
+};
+
+struct WgradParams {
+  MlpShape sh;
+  float* dP[kMaxLayers + 1];
+  const WgradItem* items;
+  StepState* st;
+};
+
+struct SparseArgs {
+  float* fm_v; float* v_s0; float* v_s1;
+  float* fm_w; float* w_s0; float* w_s1;
+  float* G; float* Gw;
+  int* slot_of; const int* uniq_ids;
+  StepState* st;
+  int Ke;
+  long long V;
+  float grad_scale;
+};
+
+// launchers (one per translation unit)
+int launch_embed_fm_fwd(const int*, const float*, const float*, const float*, const float*, __nv_bfloat16*, int,
+                        float*, float*, int, int, int, StepState*, int*, int*, int, cudaStream_t);
+int launch_fill_ones_column(__nv_bfloat16*, int, int, int, cudaStream_t);
+int mlp_fwd_plan(const MlpShape&, int*, int*, int*);
+int mlp_fwd_set_smem(int);
+int launch_mlp_fwd(const FwdMaps&, const FwdParams&, int, int, cudaStream_t);
+int mlp_bwd_plan(const MlpShape&, int*, int*, int*);
+int mlp_bwd_set_smem(int);
+int launch_mlp_bwd_chain(const BwdMaps&, const BwdParams&, int, int, cudaStream_t);
+int launch_embed_bwd(const BwdMaps&, const BwdParams&, int, cudaStream_t);
+int wgrad_set_smem();
+int launch_wgrad(const WgradMaps&, const WgradParams&, int, cudaStream_t);
+int launch_set_state(StepState*, int, float, int, int, cudaStream_t);
+int launch_dense_opt(float*, float*, float*, float*, __nv_bfloat16*, int, const StepState*, const OptHyper&, float,
+                     cudaStream_t);
+int launch_cast_weights(const float*, __nv_bfloat16*, int, cudaStream_t);
+int launch_sparse_apply(const SparseArgs&, const OptHyper&, int, bool, cudaStream_t);
+
+}  // namespace dfm

@@ -1,0 +1,211 @@
+// Optimizer kernels (tf.train.{Adam,Adagrad,Momentum,Ftrl,GradientDescent}Optimizer,
+// HVD.py:281-294) for the two kinds of state:
+//
+//   dense_opt_kernel     all MLP / out-layer / fm_bias parameters as one flat fp32 vector:
+//                        apply, refresh the bf16 tensor-core copy, zero the gradient.
+//   sparse_apply_kernel  "lazy" update of fm_v / fm_w: one warp per distinct id touched by the
+//                        batch; reads the reduced row gradient from the slot buffer, adds the
+//                        L2 term of the touched row, applies, clears the slot bookkeeping.
+//   table_dense_kernel   "dense_exact" update: every row every step with g = sparse + l2*row,
+//                        which is the math the reference's l2_loss(whole table) implies
+//                        (HVD.py:266-267).
+#include "engine.cuh"
+
+namespace dfm {
+
+__global__ void set_state_kernel(StepState* st, int count, float lr, int train, int step) {
+  st->count = count;
+  st->lr = lr;
+  st->train = train;
+  if (step >= 0) st->step = step;
+}
+
+// n = number of flat dense parameters; element n-1 is fm_bias whose gradient equals that of
+// b_out (element n-2): y = fm_bias + ... + b_out.
+__global__ void __launch_bounds__(256)
+dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restrict__ s1,
+                 float* __restrict__ grad, __nv_bfloat16* __restrict__ Wb, int n,
+                 const StepState* __restrict__ st, const OptHyper hyper, float grad_scale) {
+  const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
+    const float g = grad[i] * grad_scale;
+    grad[i] = 0.f;
+    float p = P[i], a = s0[i], b = s1[i];
+    opt_apply(c, g, p, a, b);
+    P[i] = p; s0[i] = a; s1[i] = b;
+    Wb[i] = __float2bfloat16(p);
+    if (i == n - 2) {   // fm_bias shares b_out's gradient
+      float p2 = P[n - 1], a2 = s0[n - 1], b2 = s1[n - 1];
+      opt_apply(c, g, p2, a2, b2);
+      P[n - 1] = p2; s0[n - 1] = a2; s1[n - 1] = b2;
+    }
+  }
+}
+
+__global__ void cast_weights_kernel(const float* __restrict__ P, __nv_bfloat16* __restrict__ Wb, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    Wb[i] = __float2bfloat16(P[i]);
+}
+
+
+__global__ void __launch_bounds__(256)
+sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
+  const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
+  const int n = a.st->n_unique;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < n; s += warps) {
+    const int id = a.uniq_ids[s];
+    for (int k = lane; k < a.Ke; k += 32) {
+      const size_t gi = size_t(s) * a.Ke + k, pi = size_t(id) * a.Ke + k;
+      float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
+      const float g = a.G[gi] * a.grad_scale + hyper.l2_reg * p;
+      a.G[gi] = 0.f;
+      opt_apply(c, g, p, m, v);
+      a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
+    }
+    if (lane == 0) {
+      float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
+      const float g = a.Gw[s] * a.grad_scale + hyper.l2_reg * p;
+      a.Gw[s] = 0.f;
+      opt_apply(c, g, p, m, v);
+      a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
+      a.slot_of[id] = -1;
+    }
+  }
+  // the last CTA to finish closes the step
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&a.st->sparse_done, 1) == int(gridDim.x) - 1) {
+      a.st->n_unique = 0;
+      a.st->sparse_done = 0;
+      a.st->step += 1;
+      __threadfence();
+    }
+  }
+}
+
+// dense_exact: one warp per table row, all rows.
+__global__ void __launch_bounds__(256)
+table_dense_kernel(const SparseArgs a, const OptHyper hyper) {
+  const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
+  const int lane = threadIdx.x & 31;
+  const long long warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long id = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; id < a.V; id += warps) {
+    const int s = a.slot_of[id];
+    for (int k = lane; k < a.Ke; k += 32) {
+      const size_t pi = size_t(id) * a.Ke + k;
+      float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
+      float g = hyper.l2_reg * p;
+      if (s >= 0) {
+        g += a.G[size_t(s) * a.Ke + k] * a.grad_scale;
+        a.G[size_t(s) * a.Ke + k] = 0.f;
+      }
+      opt_apply(c, g, p, m, v);
+      a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
+    }
+    __syncwarp();
+    if (lane == 0) {
+      float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
+      float g = hyper.l2_reg * p;
+      if (s >= 0) {
+        g += a.Gw[s] * a.grad_scale;
+        a.Gw[s] = 0.f;
+        a.slot_of[id] = -1;
+      }
+      opt_apply(c, g, p, m, v);
+      a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&a.st->sparse_done, 1) == int(gridDim.x) - 1) {
+      a.st->n_unique = 0;
+      a.st->sparse_done = 0;
+      a.st->step += 1;
+      __threadfence();
+    }
+  }
+}
+
+// ---- streaming AUC accumulators, tf.metrics.auc(num_thresholds=200) (HVD.py:271) ----
+// bucket(p) = number of thresholds t_j with p > t_j, thresholds = {-eps, 1/199 .. 198/199, 1+eps}.
+// hist[0][k] counts positives, hist[1][k] negatives; TP_j = sum_{k>j} hist[0][k].
+__global__ void __launch_bounds__(256)
+auc_hist_kernel(const float* __restrict__ prob, const float* __restrict__ label, int n,
+                unsigned long long* __restrict__ hist, int num_thresholds) {
+  extern __shared__ unsigned int sh[];   // 2 * (num_thresholds + 1)
+  const int nb = num_thresholds + 1;
+  for (int i = threadIdx.x; i < 2 * nb; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const float eps = 1e-7f;
+  const float scale = float(num_thresholds - 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float pr = prob[i];
+    // thresholds: t_0 = -eps, t_j = j/(T-1) for 1 <= j <= T-2, t_{T-1} = 1+eps
+    int k;
+    if (!(pr > -eps)) k = 0;
+    else if (pr > 1.f + eps) k = num_thresholds;
+    else {
+      int j = int(ceilf(pr * scale)) - 1;          // largest j with j/(T-1) < pr, approximately
+      j = max(0, min(num_thresholds - 2, j));
+      while (j + 1 <= num_thresholds - 2 && pr > float(j + 1) / scale) ++j;
+      while (j >= 1 && !(pr > float(j) / scale)) --j;
+      k = j + 1;                                   // t_0 .. t_j are below pr
+    }
+    atomicAdd(&sh[(label[i] > 0.5f ? 0 : nb) + k], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * nb; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], static_cast<unsigned long long>(sh[i]));
+}
+
+// ---------------------------------------------------------------------------------------------
+int launch_set_state(StepState* st, int count, float lr, int train, int step, cudaStream_t stream) {
+  set_state_kernel<<<1, 1, 0, stream>>>(st, count, lr, train, step);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+int launch_dense_opt(float* P, float* s0, float* s1, float* grad, __nv_bfloat16* Wb, int n, const StepState* st,
+                     const OptHyper& h, float grad_scale, cudaStream_t stream) {
+  const int grid = std::min(148 * 4, ceil_div(n, 256));
+  dense_opt_kernel<<<grid, 256, 0, stream>>>(P, s0, s1, grad, Wb, n, st, h, grad_scale);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+int launch_cast_weights(const float* P, __nv_bfloat16* Wb, int n, cudaStream_t stream) {
+  cast_weights_kernel<<<std::min(148 * 4, ceil_div(n, 256)), 256, 0, stream>>>(P, Wb, n);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+int launch_sparse_apply(const SparseArgs& a, const OptHyper& h, int max_rows, bool dense_exact, cudaStream_t stream) {
+  if (dense_exact) {
+    const long long warps_needed = a.V;
+    const int grid = int(std::min<long long>(148 * 8, (warps_needed + 7) / 8));
+    table_dense_kernel<<<grid, 256, 0, stream>>>(a, h);
+  } else {
+    const int grid = std::max(1, std::min(148 * 4, ceil_div(max_rows, 8)));
+    sparse_apply_kernel<<<grid, 256, 0, stream>>>(a, h);
+  }
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+}  // namespace dfm
+
+extern "C" int dfm_auc_hist(const float* prob, const float* label, int n, unsigned long long* hist,
+                            int num_thresholds, dfm_stream_t stream) {
+  using namespace dfm;
+  DFM_REQUIRE(num_thresholds >= 3 && num_thresholds <= 4096, "dfm_auc_hist: num_thresholds %d out of range", num_thresholds);
+  if (n <= 0) return DFM_OK;
+  const int grid = std::min(148, ceil_div(n, 256));
+  auc_hist_kernel<<<grid, 256, 2 * (num_thresholds + 1) * sizeof(unsigned int), static_cast<cudaStream_t>(stream)>>>(
+      prob, label, n, hist, num_thresholds);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}

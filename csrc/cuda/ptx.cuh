@@ -60,7 +60,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // Bounded wait.  `tag` identifies the call site in the watchdog message.
-__device__ __noinline__ void watchdog_trip(int tag) {
+static __device__ __noinline__ void watchdog_trip(int tag) {
   printf("[dfm watchdog] block (%d,%d) thread %d stuck at wait tag %d\n", blockIdx.x, blockIdx.y,
          threadIdx.x, tag);
   __trap();

@@ -1,0 +1,302 @@
+"""Python face of the native step engine (csrc/cuda/engine.cu).
+
+``FusedEngine`` owns the parameters and optimizer slots as torch CUDA tensors, hands their
+pointers to libdfm_cuda.so, and drives one fused training step (7 kernel launches: embed+FM
+forward, tcgen05 MLP forward, tcgen05 backward chain, embedding-gradient GEMM+scatter,
+split-K weight gradients, dense optimizer, sparse lazy optimizer) -- the work of one
+``session.run(train_op)`` in the reference loop (HVD.py:430-435).
+
+Dense parameters live in ONE flat fp32 vector ``[P_0 | ... | P_{L-1} | P_out | fm_bias]`` with
+``P_l = [K_l + 1, N_l]`` (weights, then the bias as last row); TF-named views of it are
+exposed by :meth:`variables` so checkpoints keep the reference's names and shapes.  Layer widths
+that are not multiples of 16 are zero-padded internally (padding units have zero weights, zero
+bias, zero gradient, so they stay exactly zero under every optimizer here).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from collections import OrderedDict
+from typing import Dict, Optional
+
+import torch
+
+from .. import _native
+from ..models.deepfm import DeepFM, DeepFMConfig
+from ..utils.optimizers import OPT_IDS, _SLOT_INIT, _SLOT_NAMES, canonical_optimizer
+
+MAX_LAYERS = 6
+
+
+class _EngineConfig(C.Structure):
+    _fields_ = [
+        ("batch_max", C.c_int32), ("field_size", C.c_int32), ("embedding_size", C.c_int32), ("n_layers", C.c_int32),
+        ("layers", C.c_int32 * MAX_LAYERS), ("keep_prob", C.c_float * MAX_LAYERS),
+        ("feature_size", C.c_int64), ("optimizer", C.c_int32), ("table_update_mode", C.c_int32),
+        ("lr", C.c_float), ("l2_reg", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+        ("momentum", C.c_float), ("ftrl_lr_power", C.c_float), ("ftrl_l1", C.c_float), ("ftrl_l2", C.c_float),
+        ("seed", C.c_uint64),
+    ]
+
+
+class _EngineTensors(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "fm_w", "fm_w_s0", "fm_w_s1", "fm_v", "fm_v_s0", "fm_v_s1", "dense", "dense_s0", "dense_s1")]
+
+
+class _DevMem:
+    """Zero-copy window onto engine-owned device memory (via __cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, n: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def _round_up(a: int, b: int) -> int:
+    return (a + b - 1) // b * b
+
+
+def fused_engine_supported(cfg: DeepFMConfig) -> Optional[str]:
+    """None if the fused kernels cover this configuration, else the reason they do not."""
+    if cfg.batch_norm:
+        return "batch_norm needs batch-wide statistics between layers; it runs on the layered path"
+    if cfg.loss_type != "log_loss":
+        return "the fused loss epilogue implements log_loss only"
+    if cfg.embedding_size % 16 or cfg.embedding_size > 128:
+        return "embedding_size must be a multiple of 16 and <= 128"
+    if not 1 <= len(cfg.deep_layers) <= MAX_LAYERS:
+        return f"1..{MAX_LAYERS} deep layers"
+    if max(cfg.deep_layers) > 512:
+        return "deep layer widths must be <= 512"
+    return None
+
+
+class FusedEngine:
+    def __init__(self, cfg: DeepFMConfig, batch_max: int, optimizer: str = "Adam", lr: float = 5e-4,
+                 table_update_mode: str = "lazy", seed: int = 0, device: Optional[torch.device] = None,
+                 beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, momentum: float = 0.95,
+                 ftrl_lr_power: float = -0.5, ftrl_l1: float = 0.0, ftrl_l2: float = 0.0):
+        why = fused_engine_supported(cfg)
+        if why:
+            raise ValueError(f"fused engine does not cover this configuration: {why}")
+        if not torch.cuda.is_available():
+            raise RuntimeError("FusedEngine needs a CUDA device (sm_100a)")
+        self.cfg = cfg
+        self.device = torch.device(device or f"cuda:{torch.cuda.current_device()}")
+        self.batch_max = int(batch_max)
+        self.opt_kind = canonical_optimizer(optimizer)
+        self.lr = float(lr)
+        self.table_update_mode = table_update_mode
+        self._lib = _native.cuda()
+        self._type_lib()
+
+        L = len(cfg.deep_layers)
+        self.L = L
+        self.Np = [_round_up(n, 16) for n in cfg.deep_layers]           # padded widths
+        self.K = [cfg.field_size * cfg.embedding_size] + self.Np        # K[l] input width of layer l
+        self.N = self.Np + [1]
+        self.off = []
+        o = 0
+        for l in range(L + 1):
+            self.off.append(o)
+            o += (self.K[l] + 1) * self.N[l]
+        self.off.append(o)            # fm_bias
+        self.n_dense = o + 1
+
+        dev, f32 = self.device, torch.float32
+        V, Ke = cfg.feature_size, cfg.embedding_size
+        i0, i1 = _SLOT_INIT[self.opt_kind]
+        self.fm_w = torch.zeros(V, device=dev, dtype=f32)
+        self.fm_v = torch.zeros(V, Ke, device=dev, dtype=f32)
+        self.dense = torch.zeros(self.n_dense, device=dev, dtype=f32)
+        self.fm_w_s0, self.fm_w_s1 = torch.full_like(self.fm_w, i0), torch.full_like(self.fm_w, i1)
+        self.fm_v_s0, self.fm_v_s1 = torch.full_like(self.fm_v, i0), torch.full_like(self.fm_v, i1)
+        self.dense_s0, self.dense_s1 = torch.full_like(self.dense, i0), torch.full_like(self.dense, i1)
+
+        ec = _EngineConfig()
+        ec.batch_max, ec.field_size, ec.embedding_size, ec.n_layers = self.batch_max, cfg.field_size, Ke, L
+        for l in range(L):
+            ec.layers[l] = self.Np[l]
+            ec.keep_prob[l] = float(cfg.dropout_keep[l])
+        ec.feature_size = V
+        ec.optimizer = OPT_IDS[self.opt_kind]
+        ec.table_update_mode = {"lazy": 0, "dense_exact": 1}[table_update_mode]
+        ec.lr, ec.l2_reg = self.lr, cfg.l2_reg
+        ec.beta1, ec.beta2, ec.eps, ec.momentum = beta1, beta2, eps, momentum
+        ec.ftrl_lr_power, ec.ftrl_l1, ec.ftrl_l2 = ftrl_lr_power, ftrl_l1, ftrl_l2
+        ec.seed = seed & 0xFFFFFFFFFFFFFFFF
+        et = _EngineTensors(*[t.data_ptr() for t in (
+            self.fm_w, self.fm_w_s0, self.fm_w_s1, self.fm_v, self.fm_v_s0, self.fm_v_s1,
+            self.dense, self.dense_s0, self.dense_s1)])
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _native.check(self._lib.dfm_engine_create(C.byref(ec), C.byref(et), C.byref(h)), "dfm_engine_create")
+        self._h = h
+        self._bufs: Dict[str, torch.Tensor] = {}
+        self.state_t = self.buffer("state", dtype="i4")   # raw int32 view of StepState
+
+    # ------------------------------------------------------------------ plumbing
+    def _type_lib(self):
+        lib = self._lib
+        if getattr(lib, "_engine_typed", False):
+            return
+        lib.dfm_engine_create.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+        lib.dfm_engine_destroy.argtypes = [C.c_void_p]
+        lib.dfm_engine_set_state.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p]
+        lib.dfm_engine_sync_weights.argtypes = [C.c_void_p, C.c_void_p]
+        lib.dfm_engine_forward.argtypes = [C.c_void_p] * 5
+        lib.dfm_engine_train_step.argtypes = [C.c_void_p] * 5
+        lib.dfm_engine_buffer.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong)]
+        lib.dfm_engine_launches_per_step.argtypes = [C.c_void_p]
+        lib.dfm_auc_hist.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        lib._engine_typed = True
+
+    def _stream(self) -> C.c_void_p:
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def buffer(self, name: str, index: int = 0, dtype: str = "f4") -> torch.Tensor:
+        """Zero-copy torch view of an engine buffer (dtype: 'f4', 'i4', or 'bf16')."""
+        key = f"{name}:{index}:{dtype}"
+        if key not in self._bufs:
+            p, n = C.c_void_p(), C.c_longlong()
+            _native.check(self._lib.dfm_engine_buffer(self._h, name.encode(), index, C.byref(p), C.byref(n)),
+                          "dfm_engine_buffer")
+            typestr = {"f4": "<f4", "i4": "<i4", "bf16": "<i2"}[dtype]
+            t = torch.as_tensor(_DevMem(p.value, n.value, typestr), device=self.device)
+            if dtype == "bf16":
+                t = t.view(torch.bfloat16)
+            self._bufs[key] = t
+        return self._bufs[key]
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.dfm_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ parameters
+    def _layer_views(self, flat: torch.Tensor, l: int):
+        """(weights [K_l, N_l], bias [N_l]) views of layer l inside a flat dense vector."""
+        K, N, o = self.K[l], self.N[l], self.off[l]
+        return flat[o:o + K * N].view(K, N), flat[o + K * N:o + (K + 1) * N]
+
+    @torch.no_grad()
+    def load_from_module(self, m: DeepFM) -> None:
+        cfg = self.cfg
+        self.fm_w.copy_(m.fm_w.detach())
+        self.fm_v.copy_(m.fm_v.detach())
+        self.dense.zero_()
+        k_prev = cfg.field_size * cfg.embedding_size
+        for l in range(self.L):
+            w, b = self._layer_views(self.dense, l)
+            n = cfg.deep_layers[l]
+            w[:k_prev, :n] = m.mlp_w[l].detach()
+            b[:n] = m.mlp_b[l].detach()
+            k_prev = n
+        w, b = self._layer_views(self.dense, self.L)
+        w[:k_prev, :] = m.out_w.detach()
+        b[:] = m.out_b.detach()
+        self.dense[self.off[self.L + 1]] = m.fm_bias.detach()[0]
+        self.sync_weights()
+
+    @torch.no_grad()
+    def store_to_module(self, m: DeepFM) -> None:
+        m.load_tf_variables({k: v for k, v in self.variables().items()}, strict=True)
+
+    def variables(self) -> "OrderedDict[str, torch.Tensor]":
+        """TF-named parameter tensors (unpadded views / slices of the engine's storage)."""
+        return self._named(self.fm_w, self.fm_v, self.dense)
+
+    def _named(self, fm_w, fm_v, dense) -> "OrderedDict[str, torch.Tensor]":
+        cfg = self.cfg
+        d: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+        d["fm_bias"] = dense[self.off[self.L + 1]:self.off[self.L + 1] + 1]
+        d["fm_w"] = fm_w
+        d["fm_v"] = fm_v
+        k_prev = cfg.field_size * cfg.embedding_size
+        for l in range(self.L):
+            w, b = self._layer_views(dense, l)
+            n = cfg.deep_layers[l]
+            d[f"Deep-part/mlp{l}/weights"] = w[:k_prev, :n]
+            d[f"Deep-part/mlp{l}/biases"] = b[:n]
+            k_prev = n
+        w, b = self._layer_views(dense, self.L)
+        d["Deep-part/deep_out/weights"] = w[:k_prev, :]
+        d["Deep-part/deep_out/biases"] = b
+        return d
+
+    def slot_variables(self) -> "OrderedDict[str, torch.Tensor]":
+        """Optimizer slots under TF checkpoint names (``<var>/Adam`` ...)."""
+        n0, n1 = _SLOT_NAMES[self.opt_kind]
+        out: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+        for suffix, (w, v, dn) in ((n0, (self.fm_w_s0, self.fm_v_s0, self.dense_s0)),
+                                   (n1, (self.fm_w_s1, self.fm_v_s1, self.dense_s1))):
+            if suffix is None:
+                continue
+            for k, t in self._named(w, v, dn).items():
+                out[f"{k}/{suffix}"] = t
+        return out
+
+    def sync_weights(self) -> None:
+        """Call after writing to ``dense`` from Python (init, restore, broadcast)."""
+        _native.check(self._lib.dfm_engine_sync_weights(self._h, self._stream()), "dfm_engine_sync_weights")
+
+    # ------------------------------------------------------------------ stepping
+    def set_state(self, count: int, train: bool, lr: Optional[float] = None, step: int = -1) -> None:
+        _native.check(self._lib.dfm_engine_set_state(self._h, int(count), float(self.lr if lr is None else lr),
+                                                     int(train), int(step), self._stream()), "dfm_engine_set_state")
+
+    def _check_inputs(self, ids, vals, labels):
+        assert ids.is_cuda and ids.dtype == torch.int32 and ids.is_contiguous(), "feat_ids must be contiguous int32 CUDA"
+        assert vals.is_cuda and vals.dtype == torch.float32 and vals.is_contiguous()
+        assert ids.shape == vals.shape and ids.shape[1] == self.cfg.field_size and ids.shape[0] <= self.batch_max
+        if labels is not None:
+            assert labels.is_cuda and labels.dtype == torch.float32 and labels.numel() == ids.shape[0]
+
+    def forward(self, ids: torch.Tensor, vals: torch.Tensor, labels: Optional[torch.Tensor] = None,
+                set_state: bool = True) -> torch.Tensor:
+        """Inference forward; returns the probability buffer view ``[count]`` (valid until the next call)."""
+        self._check_inputs(ids, vals, labels)
+        n = ids.shape[0]
+        if set_state:
+            self.set_state(n, train=False)
+        _native.check(self._lib.dfm_engine_forward(self._h, ids.data_ptr(), vals.data_ptr(),
+                                                   labels.data_ptr() if labels is not None else None,
+                                                   self._stream()), "dfm_engine_forward")
+        return self.buffer("prob")[:n]
+
+    def train_step(self, ids: torch.Tensor, vals: torch.Tensor, labels: torch.Tensor, set_state: bool = True) -> None:
+        """One optimizer step on the batch.  Asynchronous; read :meth:`loss` afterwards if needed."""
+        self._check_inputs(ids, vals, labels)
+        if set_state:
+            self.set_state(ids.shape[0], train=True)
+        _native.check(self._lib.dfm_engine_train_step(self._h, ids.data_ptr(), vals.data_ptr(), labels.data_ptr(),
+                                                      self._stream()), "dfm_engine_train_step")
+
+    # StepState field order: count, step, lr, loss_sum, n_unique, sparse_done, train, pad
+    def loss_sum_tensor(self) -> torch.Tensor:
+        return self.state_t.view(torch.float32)[3:4]
+
+    def step_tensor(self) -> torch.Tensor:
+        return self.state_t[1:2]
+
+    def read_state(self) -> Dict[str, float]:
+        s = self.state_t.cpu()
+        f = s.view(torch.float32)
+        return {"count": int(s[0]), "step": int(s[1]), "lr": float(f[2]), "loss_sum": float(f[3]),
+                "n_unique": int(s[4]), "train": int(s[6])}
+
+    def launches_per_step(self) -> int:
+        return int(self._lib.dfm_engine_launches_per_step(self._h))
+
+
+def auc_histogram(prob: torch.Tensor, label: torch.Tensor, hist: torch.Tensor, num_thresholds: int = 200) -> None:
+    """Accumulates tf.metrics.auc-style confusion buckets on the GPU (csrc/cuda/optim.cu)."""
+    assert prob.is_cuda and hist.dtype == torch.int64 and hist.numel() == 2 * (num_thresholds + 1)
+    lib = _native.cuda()
+    lib.dfm_auc_hist.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+    _native.check(lib.dfm_auc_hist(prob.data_ptr(), label.data_ptr(), prob.numel(), hist.data_ptr(), num_thresholds,
+                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)), "dfm_auc_hist")

@@ -42,6 +42,75 @@ int dfm_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb
                   float* C, int ldc, int M, int N, int K, const float* bias, int relu,
                   dfm_stream_t stream);
 
+
+/* ------------------------------------------------------------------------
+ * Optimizers (tf.train.*Optimizer of HVD.py:281-294) and table update modes
+ * ---------------------------------------------------------------------- */
+#define DFM_OPT_ADAM 0
+#define DFM_OPT_ADAGRAD 1
+#define DFM_OPT_MOMENTUM 2
+#define DFM_OPT_FTRL 3
+#define DFM_OPT_GD 4
+
+#define DFM_TABLE_LAZY 0        /* touched rows only (sparse-gradient path)            */
+#define DFM_TABLE_DENSE_EXACT 1 /* every row every step, g = sparse + l2*row (HVD.py:266-267) */
+
+#define DFM_MAX_LAYERS 6
+
+typedef struct {
+  int32_t batch_max;       /* per-GPU batch capacity                                       */
+  int32_t field_size;      /* F   (--field_size)                                            */
+  int32_t embedding_size;  /* K   (--embedding_size), multiple of 16, <= 128                */
+  int32_t n_layers;        /* hidden layers of the deep tower (--deep_layers)               */
+  int32_t layers[DFM_MAX_LAYERS];   /* widths, multiples of 16, <= 512                      */
+  float keep_prob[DFM_MAX_LAYERS];  /* --dropout values are KEEP probabilities (HVD.py:235) */
+  int64_t feature_size;    /* V   (--feature_size), rows of fm_w / fm_v                     */
+  int32_t optimizer;       /* DFM_OPT_*                                                     */
+  int32_t table_update_mode; /* DFM_TABLE_*                                                 */
+  float lr;                /* already scaled by world size (HVD.py:171)                     */
+  float l2_reg;            /* applies to fm_w and fm_v only (HVD.py:266-267)                */
+  float beta1, beta2, eps; /* Adam                                                          */
+  float momentum;          /* Momentum                                                      */
+  float ftrl_lr_power, ftrl_l1, ftrl_l2;
+  uint64_t seed;           /* dropout stream                                                */
+} dfm_engine_config;
+
+/* Caller-owned fp32 device tensors (parameters and their optimizer slots).
+ * dense* are flat vectors laid out as
+ *   [P_0 | P_1 | ... | P_{L-1} | P_out | fm_bias],  P_l = [K_l + 1, N_l] row-major,
+ * rows 0..K_l-1 = Deep-part/mlp{l}/weights, row K_l = .../biases (P_out: deep_out). */
+typedef struct {
+  float* fm_w;    float* fm_w_s0;  float* fm_w_s1;    /* [V]        */
+  float* fm_v;    float* fm_v_s0;  float* fm_v_s1;    /* [V, K]     */
+  float* dense;   float* dense_s0; float* dense_s1;   /* [n_dense]  */
+} dfm_engine_tensors;
+
+int dfm_engine_create(const dfm_engine_config* cfg, const dfm_engine_tensors* tensors, void** engine);
+int dfm_engine_destroy(void* engine);
+/* offsets[L+2] (P_0..P_out, fm_bias) in elements, pitches[L+1] of the activation buffers. */
+int dfm_engine_layout(void* engine, long long* offsets, int* pitches, int* n_dense, int* batch_pad);
+/* Step scalars live on the device (graph-replay safe): valid rows, lr, train flag;
+ * step >= 0 also resets the 1-based optimizer step counter. */
+int dfm_engine_set_state(void* engine, int count, float lr, int train, int step, dfm_stream_t stream);
+/* Refresh the bf16 tensor-core copy after the caller changed `dense` (init, restore, broadcast). */
+int dfm_engine_sync_weights(void* engine, dfm_stream_t stream);
+/* Forward only: embed+FM kernel, fused MLP kernel.  ids int32 [B,F], vals f32 [B,F],
+ * labels f32 [B] or NULL.  Results in the "prob"/"logit" buffers, loss sum in "state". */
+int dfm_engine_forward(void* engine, const int* ids, const float* vals, const float* labels,
+                       dfm_stream_t stream);
+/* Forward + backward + optimizer update of every parameter (one reference train_op). */
+int dfm_engine_train_step(void* engine, const int* ids, const float* vals, const float* labels,
+                          dfm_stream_t stream);
+int dfm_engine_launches_per_step(void* engine);
+/* Device pointer + element count of an internal buffer:
+ * "prob","logit","dlogit","fm_part","s_sum","state","dense_grad","dense_bf16","G","Gw",
+ * "uniq_ids","slot_of", and "act"/"dz" with a layer index. */
+int dfm_engine_buffer(void* engine, const char* name, int index, void** ptr, long long* n_elems);
+
+/* tf.metrics.auc accumulators (HVD.py:271): hist[2][num_thresholds+1] uint64, row 0 positives. */
+int dfm_auc_hist(const float* prob, const float* label, int n, unsigned long long* hist,
+                 int num_thresholds, dfm_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
