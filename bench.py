@@ -1,0 +1,232 @@
+#!/usr/bin/env python
+"""Headline benchmark: DeepFM training throughput (examples/s) on N B200s.
+
+Config (BASELINE.json config 2 / the reference's script defaults, HVD.py:36-50): 39 fields,
+feature_size 117,581, embedding 32, MLP 256-128-64, dropout keep 0.5, Adam lr 5e-4 x N, l2 1e-4,
+batch 2048 per GPU, synchronous data parallel, replicated embedding table with sparse gradients.
+Data: synthetic Criteo-shaped TFRecords written and parsed by the framework's own native IO
+layer, random-initialised weights.
+
+  python bench.py --gpus 1 --steps 200 --warmup 20
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+         --master-port 29511 bench.py --gpus 8 --steps 200 --warmup 20
+
+Prints ONE JSON line (rank 0).  `value` times the device work of K full training steps (forward,
+backward, optimizer for every parameter) with CUDA events, max over ranks; `e2e.value` times the
+same K steps through the public Trainer API including, every step, the pinned-host -> device copy
+of that step's batch and a device -> host read of its loss.
+`--impl reference` reports that the unmodified TF1/Horovod reference cannot run in this image;
+`--impl eager` runs the stock PyTorch (+NCCL) restatement used as the measured baseline.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FIELD, FEATURE, EMB = 39, 117581, 32
+LAYERS = (256, 128, 64)
+KEEP = (0.5, 0.5, 0.5)
+BATCH = 2048
+LR, L2 = 5e-4, 1e-4
+POOL = 256          # distinct batches cycled through: 256 x 647 KB = 166 MB > the 126 MB L2
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="fused", choices=["fused", "reference", "eager"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--pool", type=int, default=POOL)
+    ap.add_argument("--no-graph", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.t.join(timeout=1)
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 6:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_host_pool(batch: int, pool: int, rank: int, world: int):
+    """Synthetic Criteo-shaped TFRecords -> native loader -> list of pinned batch slabs."""
+    import torch
+    from deepfm_b200.data.loader import BatchLoader, alloc_slab
+    from deepfm_b200.data.tfrecord import generate_synthetic
+    n = batch * pool
+    path = os.path.join(tempfile.gettempdir(), f"dfm_bench_r{rank}_{n}.tfrecords")
+    if not os.path.exists(path):
+        generate_synthetic(path + ".tmp", n, FIELD, FEATURE, n_dense=13, seed=1234 + rank, pos_rate=0.2553, zipf_s=1.05)
+        os.replace(path + ".tmp", path)
+    slabs = []
+    loader = BatchLoader([path], FIELD, batch, num_epochs=1, drop_remainder=True, num_workers=8, num_slots=4,
+                         ids_dtype=torch.int32, verify_crc=True)
+    t0 = time.time()
+    for hb in loader:
+        slab, ids, vals, labels = alloc_slab(batch, FIELD, torch.int32, pin_memory=True)
+        slab.copy_(hb.slab)
+        slabs.append((slab, ids, vals, labels))
+    parse_s = time.time() - t0
+    loader.close()
+    return slabs, n / max(parse_s, 1e-9)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "reference is two TF1.14/1.15 + Horovod + sagemaker_tensorflow scripts with no setup.py; "
+                          "TensorFlow 1.x has no wheel for Python 3.12/CUDA 12.9 and none is in /opt/wheelhouse "
+                          "(see DESIGN.md, BASELINE.md section 2)"}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit(f"--gpus {args.gpus} needs a torchrun launch with {args.gpus} processes")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from deepfm_b200.models.deepfm import DeepFMConfig
+    from deepfm_b200.runtime.trainer import Trainer, TrainerOptions
+
+    cfg = DeepFMConfig(field_size=FIELD, feature_size=FEATURE, embedding_size=EMB, deep_layers=LAYERS,
+                       dropout_keep=KEEP, l2_reg=L2)
+    opts = TrainerOptions(batch_size=args.batch, optimizer="Adam", learning_rate=LR, table_update_mode="lazy",
+                          backend="fused" if args.impl == "fused" else "eager", seed=1,
+                          cuda_graph=not args.no_graph, scale_lr_by_world=True)
+    trainer = Trainer(cfg, opts, device=dev)
+
+    pool, parse_rate = make_host_pool(args.batch, args.pool, rank, world)
+    K, W = args.steps, max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-timed: inputs rotate through a device-resident pool ----------------
+    dev_pool = [s[0].to(dev, non_blocking=True) for s in pool]
+    torch.cuda.synchronize()
+    for i in range(W):
+        trainer.train_step_device(dev_pool[i % len(dev_pool)])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(K):
+        trainer.train_step_device(dev_pool[(W + i) % len(dev_pool)])
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_dev = e0.elapsed_time(e1)
+    del dev_pool
+
+    # ---------------- end to end: pinned host -> device every step, loss back to host ----------------
+    for i in range(W):
+        trainer.train_step_host(pool[i % len(pool)][0])
+    trainer.last_loss()
+    barrier()
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    h0.record()
+    loss_acc = 0.0
+    for i in range(K):
+        trainer.train_step_host(pool[(W + i) % len(pool)][0])
+        loss_acc += trainer.last_loss()          # D2H read of the previous step's loss (pipelined by one step)
+    final_loss = trainer.last_loss(wait_current=True)
+    h1.record()
+    barrier()
+    ms_e2e = h0.elapsed_time(h1)
+
+    t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_dev, ms_e2e = t.tolist()
+    global_batch = args.batch * world
+    value = global_batch * K / (ms_dev / 1e3)
+    e2e = global_batch * K / (ms_e2e / 1e3)
+    slab_bytes = pool[0][0].numel()
+    out = {
+        "metric": "train_examples_per_sec", "value": value, "unit": "examples/s", "n_gpus": world, "steps": K,
+        "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16" if args.impl == "fused" else "fp32", "data": "synthetic",
+        "impl": args.impl,
+        "config": {"model": "DeepFM F39 K32 V117581 MLP256-128-64 dropout0.5 Adam lazy-sparse",
+                   "global_batch": global_batch, "seq_len": FIELD, "parallelism": f"dp{world}",
+                   "l2": f"inputs rotate through {len(pool)} distinct batches ({len(pool) * slab_bytes / 1e6:.0f} MB > L2)",
+                   "backend": trainer.backend, "cuda_graph": trainer.uses_graph},
+        "clocks": clocks,
+        "e2e": {"value": e2e, "unit": "examples/s", "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": slab_bytes,
+                "d2h_bytes_per_step": 4},
+        "gpu_launches": trainer.launches_per_step() * K,
+        "final_loss": final_loss, "mean_loss": loss_acc / max(K, 1),
+        "loader_records_per_sec": parse_rate,
+    }
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

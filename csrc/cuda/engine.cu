@@ -45,6 +45,15 @@ struct Engine {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 
+  // optional: the captured train step and the double-buffered host->device input pipeline
+  static constexpr int kPipe = 2;
+  cudaGraphExec_t graph[kPipe] = {nullptr, nullptr};
+  uint8_t* in_slab[kPipe] = {nullptr, nullptr};     // [ids | vals | labels] for batch_max rows
+  size_t slab_bytes = 0, off_vals = 0, off_labels = 0;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_h2d[kPipe] = {nullptr, nullptr}, ev_done[kPipe] = {nullptr, nullptr};
+  long long pipe_step = 0;
+
   template <typename T>
   int alloc(T** p, size_t n, int fill_byte = 0) {
     void* q = nullptr;
@@ -258,6 +267,12 @@ extern "C" int dfm_engine_destroy(void* h) {
   if (E->side) cudaStreamDestroy(E->side);
   if (E->ev_fork) cudaEventDestroy(E->ev_fork);
   if (E->ev_join) cudaEventDestroy(E->ev_join);
+  for (int i = 0; i < Engine::kPipe; ++i) {
+    if (E->graph[i]) cudaGraphExecDestroy(E->graph[i]);
+    if (E->ev_h2d[i]) cudaEventDestroy(E->ev_h2d[i]);
+    if (E->ev_done[i]) cudaEventDestroy(E->ev_done[i]);
+  }
+  if (E->copy_stream) cudaStreamDestroy(E->copy_stream);
   delete E;
   return DFM_OK;
 }
@@ -288,6 +303,92 @@ extern "C" int dfm_engine_train_step(void* h, const int* ids, const float* vals,
 }
 
 extern "C" int dfm_engine_launches_per_step(void* h) { (void)h; return 7; }
+
+// ---- CUDA-graph replay + double-buffered input pipeline -------------------------------------
+// Input slab layout (host and device): ids int32 [batch_max*F] | vals f32 [batch_max*F] | labels f32 [batch_max]
+extern "C" int dfm_engine_slab_layout(void* h, long long* bytes, long long* off_vals, long long* off_labels) {
+  Engine* E = static_cast<Engine*>(h);
+  const size_t bf = size_t(E->cfg.batch_max) * E->cfg.field_size;
+  *off_vals = (long long)(bf * 4);
+  *off_labels = (long long)(bf * 8);
+  *bytes = (long long)(bf * 8 + size_t(E->cfg.batch_max) * 4);
+  return DFM_OK;
+}
+
+// Captures the full train step once per input slab.  `stream` must not be the legacy default stream.
+// Uses the step state as it is at replay time (set count/lr/train first; the step counter advances on
+// the device).
+extern "C" int dfm_engine_capture(void* h, dfm_stream_t s_) {
+  Engine* E = static_cast<Engine*>(h);
+  cudaStream_t s = static_cast<cudaStream_t>(s_);
+  long long bytes, ov, ol;
+  dfm_engine_slab_layout(h, &bytes, &ov, &ol);
+  E->slab_bytes = size_t(bytes); E->off_vals = size_t(ov); E->off_labels = size_t(ol);
+  for (int i = 0; i < Engine::kPipe; ++i) {
+    if (!E->in_slab[i]) {
+      int rc = E->alloc(&E->in_slab[i], E->slab_bytes);
+      if (rc) return rc;
+    }
+    if (!E->ev_h2d[i]) {
+      DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_h2d[i], cudaEventDisableTiming));
+      DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_done[i], cudaEventDisableTiming));
+    }
+  }
+  if (!E->copy_stream) DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < Engine::kPipe; ++i) {
+    if (E->graph[i]) { cudaGraphExecDestroy(E->graph[i]); E->graph[i] = nullptr; }
+    cudaGraph_t g = nullptr;
+    DFM_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    const int* ids = reinterpret_cast<const int*>(E->in_slab[i]);
+    const float* vals = reinterpret_cast<const float*>(E->in_slab[i] + E->off_vals);
+    const float* labels = reinterpret_cast<const float*>(E->in_slab[i] + E->off_labels);
+    int rc = engine_forward(*E, ids, vals, labels, 1, s);
+    if (!rc) rc = engine_backward_update(*E, ids, vals, s);
+    cudaError_t ce = cudaStreamEndCapture(s, &g);
+    if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+    if (ce != cudaSuccess) { set_error("cudaStreamEndCapture: %s", cudaGetErrorString(ce)); return DFM_ERR_CUDA; }
+    ce = cudaGraphInstantiate(&E->graph[i], g, 0);
+    cudaGraphDestroy(g);
+    if (ce != cudaSuccess) { set_error("cudaGraphInstantiate: %s", cudaGetErrorString(ce)); return DFM_ERR_CUDA; }
+  }
+  E->pipe_step = 0;
+  return DFM_OK;
+}
+
+// Device-resident replay (inputs already in slab `which`).
+extern "C" int dfm_engine_replay(void* h, int which, dfm_stream_t s) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(which >= 0 && which < Engine::kPipe && E->graph[which], "dfm_engine_replay: capture first");
+  DFM_CUDA_CHECK(cudaGraphLaunch(E->graph[which], static_cast<cudaStream_t>(s)));
+  return DFM_OK;
+}
+
+extern "C" int dfm_engine_slab_ptr(void* h, int which, void** ptr) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(which >= 0 && which < Engine::kPipe && E->in_slab[which], "dfm_engine_slab_ptr: capture first");
+  *ptr = E->in_slab[which];
+  return DFM_OK;
+}
+
+// One end-to-end step from pinned host memory: H2D of the batch on the copy stream (overlapping the
+// previous step's kernels), graph replay on `stream`, D2H of the loss sum into `loss_host` (pinned).
+extern "C" int dfm_engine_step_from_host(void* h, const void* host_slab, float* loss_host, dfm_stream_t s_) {
+  Engine* E = static_cast<Engine*>(h);
+  cudaStream_t s = static_cast<cudaStream_t>(s_);
+  const int w = int(E->pipe_step % Engine::kPipe);
+  DFM_REQUIRE(E->graph[w] != nullptr, "dfm_engine_step_from_host: capture first");
+  // slab w was last read by step (pipe_step - kPipe)
+  if (E->pipe_step >= Engine::kPipe) DFM_CUDA_CHECK(cudaStreamWaitEvent(E->copy_stream, E->ev_done[w], 0));
+  DFM_CUDA_CHECK(cudaMemcpyAsync(E->in_slab[w], host_slab, E->slab_bytes, cudaMemcpyHostToDevice, E->copy_stream));
+  DFM_CUDA_CHECK(cudaEventRecord(E->ev_h2d[w], E->copy_stream));
+  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E->ev_h2d[w], 0));
+  DFM_CUDA_CHECK(cudaGraphLaunch(E->graph[w], s));
+  DFM_CUDA_CHECK(cudaEventRecord(E->ev_done[w], s));
+  if (loss_host)
+    DFM_CUDA_CHECK(cudaMemcpyAsync(loss_host, &E->st->loss_sum, sizeof(float), cudaMemcpyDeviceToHost, s));
+  E->pipe_step++;
+  return DFM_OK;
+}
 
 extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** ptr, long long* n_elems) {
   Engine* E = static_cast<Engine*>(h);

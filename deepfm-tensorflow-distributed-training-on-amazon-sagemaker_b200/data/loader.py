@@ -31,6 +31,25 @@ class HostBatch:
     feat_vals: torch.Tensor  # [n, F] float32
     labels: torch.Tensor     # [n]    float32
     count: int
+    slab: Optional[torch.Tensor] = None   # the whole slot as bytes: [ids | vals | labels] for batch_size rows
+
+
+def slab_layout(batch_size: int, field_size: int, ids_dtype: torch.dtype = torch.int32):
+    """(total_bytes, offset_vals, offset_labels) of a batch slab -- the layout the fused engine's
+    host->device pipeline copies in one piece (dfm_engine_slab_layout)."""
+    isz = 4 if ids_dtype == torch.int32 else 8
+    bf = batch_size * field_size
+    return bf * isz + bf * 4 + batch_size * 4, bf * isz, bf * isz + bf * 4
+
+
+def alloc_slab(batch_size: int, field_size: int, ids_dtype: torch.dtype = torch.int32, pin_memory: bool = False):
+    """One contiguous (optionally pinned) byte buffer plus typed views (ids, vals, labels) into it."""
+    total, ov, ol = slab_layout(batch_size, field_size, ids_dtype)
+    slab = torch.empty(total, dtype=torch.uint8, pin_memory=pin_memory)
+    ids = slab[:ov].view(ids_dtype).view(batch_size, field_size)
+    vals = slab[ov:ol].view(torch.float32).view(batch_size, field_size)
+    labels = slab[ol:].view(torch.float32)
+    return slab, ids, vals, labels
 
 
 class BatchLoader:
@@ -53,9 +72,10 @@ class BatchLoader:
         if pin_memory is None:
             pin_memory = torch.cuda.is_available()
         self.field_size, self.batch_size = field_size, batch_size
-        self._ids = [torch.empty((batch_size, field_size), dtype=ids_dtype, pin_memory=pin_memory) for _ in range(num_slots)]
-        self._vals = [torch.empty((batch_size, field_size), dtype=torch.float32, pin_memory=pin_memory) for _ in range(num_slots)]
-        self._labels = [torch.empty((batch_size,), dtype=torch.float32, pin_memory=pin_memory) for _ in range(num_slots)]
+        self._slabs, self._ids, self._vals, self._labels = [], [], [], []
+        for _ in range(num_slots):
+            slab, ids, vals, labels = alloc_slab(batch_size, field_size, ids_dtype, pin_memory)
+            self._slabs.append(slab); self._ids.append(ids); self._vals.append(vals); self._labels.append(labels)
         cfg = _Cfg(field_size, batch_size, max(1, num_epochs), int(drop_remainder), max(1, shard_n), shard_i,
                    num_workers, num_slots, int(ids_dtype == torch.int32), int(verify_crc), int(streaming), 0)
         arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
@@ -82,7 +102,7 @@ class BatchLoader:
             raise DataError(self._lib.dfio_last_error().decode())
         s, n = slot.value, count.value
         self._held = s
-        return HostBatch(self._ids[s][:n], self._vals[s][:n], self._labels[s][:n], n)
+        return HostBatch(self._ids[s][:n], self._vals[s][:n], self._labels[s][:n], n, self._slabs[s])
 
     def stats(self):
         r, b, y = C.c_int64(), C.c_int64(), C.c_int64()

@@ -123,6 +123,21 @@ class DeepFM(nn.Module):
         feat_ids = feat_ids.long().view(-1, cfg.field_size)
         feat_vals = feat_vals.float().view(-1, cfg.field_size)
         y_w, y_v, e = self.fm_terms(feat_ids, feat_vals)
+        return self._tower(y_w, y_v, e, training)
+
+    def forward_rows(self, w_rows: torch.Tensor, v_rows: torch.Tensor, inverse: torch.Tensor,
+                     feat_vals: torch.Tensor, training: bool = False) -> torch.Tensor:
+        """Same forward, but the table rows are passed in explicitly: ``w_rows[u]``, ``v_rows[u, K]`` are
+        the rows of the batch's distinct ids and ``inverse[B, F]`` indexes into them.  Differentiating
+        w.r.t. the rows yields the de-duplicated sparse gradient directly."""
+        feat_vals = feat_vals.float().view(-1, self.cfg.field_size)
+        y_w = (w_rows[inverse] * feat_vals).sum(1)
+        e = v_rows[inverse] * feat_vals.unsqueeze(-1)
+        y_v = 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)
+        return self._tower(y_w, y_v, e, training)
+
+    def _tower(self, y_w: torch.Tensor, y_v: torch.Tensor, e: torch.Tensor, training: bool) -> torch.Tensor:
+        cfg = self.cfg
         h = e.reshape(e.shape[0], -1)
         for i in range(len(cfg.deep_layers)):
             h = F.relu(h @ self.mlp_w[i] + self.mlp_b[i])

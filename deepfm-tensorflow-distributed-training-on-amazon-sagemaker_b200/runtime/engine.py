@@ -147,6 +147,11 @@ class FusedEngine:
         lib.dfm_engine_buffer.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong)]
         lib.dfm_engine_launches_per_step.argtypes = [C.c_void_p]
         lib.dfm_auc_hist.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        lib.dfm_engine_slab_layout.argtypes = [C.c_void_p] + [C.POINTER(C.c_longlong)] * 3
+        lib.dfm_engine_capture.argtypes = [C.c_void_p, C.c_void_p]
+        lib.dfm_engine_slab_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        lib.dfm_engine_replay.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        lib.dfm_engine_step_from_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib._engine_typed = True
 
     def _stream(self) -> C.c_void_p:
@@ -288,6 +293,38 @@ class FusedEngine:
         f = s.view(torch.float32)
         return {"count": int(s[0]), "step": int(s[1]), "lr": float(f[2]), "loss_sum": float(f[3]),
                 "n_unique": int(s[4]), "train": int(s[6])}
+
+    # ------------------------------------------------------------------ graph replay / host pipeline
+    def capture(self, count: Optional[int] = None) -> None:
+        """Records the train step as a CUDA graph (one per device input slab).  Fixes ``count`` and the
+        train flag; the optimizer step counter keeps advancing on the device."""
+        self.set_state(self.batch_max if count is None else count, train=True)
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            _native.check(self._lib.dfm_engine_capture(self._h, C.c_void_p(side.cuda_stream)), "dfm_engine_capture")
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        self._captured = True
+
+    def device_slab(self, which: int):
+        """(slab_bytes_tensor, ids, vals, labels) views of device input slab ``which`` (after capture)."""
+        p = C.c_void_p()
+        _native.check(self._lib.dfm_engine_slab_ptr(self._h, which, C.byref(p)), "dfm_engine_slab_ptr")
+        tot, ov, ol = C.c_longlong(), C.c_longlong(), C.c_longlong()
+        self._lib.dfm_engine_slab_layout(self._h, C.byref(tot), C.byref(ov), C.byref(ol))
+        slab = torch.as_tensor(_DevMem(p.value, tot.value, "|u1"), device=self.device)
+        B, Fd = self.batch_max, self.cfg.field_size
+        return (slab, slab[:ov.value].view(torch.int32).view(B, Fd), slab[ov.value:ol.value].view(torch.float32).view(B, Fd),
+                slab[ol.value:].view(torch.float32))
+
+    def replay(self, which: int = 0) -> None:
+        _native.check(self._lib.dfm_engine_replay(self._h, which, self._stream()), "dfm_engine_replay")
+
+    def step_from_host(self, host_slab: torch.Tensor, loss_host: Optional[torch.Tensor] = None) -> None:
+        """End-to-end step: pinned host slab -> device (copy stream) -> graph replay -> loss to pinned host."""
+        _native.check(self._lib.dfm_engine_step_from_host(
+            self._h, host_slab.data_ptr(), loss_host.data_ptr() if loss_host is not None else None,
+            self._stream()), "dfm_engine_step_from_host")
 
     def launches_per_step(self) -> int:
         return int(self._lib.dfm_engine_launches_per_step(self._h))

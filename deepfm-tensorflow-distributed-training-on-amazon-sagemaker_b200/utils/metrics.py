@@ -86,6 +86,16 @@ class StreamingAUC:
             self._all[0].append(labels)
             self._all[1].append(preds)
 
+    @property
+    def keep_all_enabled(self) -> bool:
+        return self._all is not None
+
+    def remember(self, labels, preds) -> None:
+        """Keeps raw (label, prediction) pairs for the exact AUC without touching the histogram."""
+        if self._all is not None:
+            self._all[0].append(np.asarray(labels, dtype=np.float32).reshape(-1).copy())
+            self._all[1].append(np.asarray(preds, dtype=np.float32).reshape(-1).copy())
+
     def add_hist(self, hist) -> None:
         self.hist += np.asarray(hist, dtype=np.int64).reshape(2, self.T + 1)
 

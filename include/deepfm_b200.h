@@ -102,6 +102,17 @@ int dfm_engine_forward(void* engine, const int* ids, const float* vals, const fl
 int dfm_engine_train_step(void* engine, const int* ids, const float* vals, const float* labels,
                           dfm_stream_t stream);
 int dfm_engine_launches_per_step(void* engine);
+
+/* CUDA-graph replay and the double-buffered input pipeline.
+ * Input slab (host and device): ids int32 [batch_max*F] | vals f32 [batch_max*F] | labels f32 [batch_max]. */
+int dfm_engine_slab_layout(void* engine, long long* bytes, long long* off_vals, long long* off_labels);
+/* Records one train step per device input slab (2 slabs) on `stream` (not the legacy default stream). */
+int dfm_engine_capture(void* engine, dfm_stream_t stream);
+int dfm_engine_slab_ptr(void* engine, int which, void** ptr);
+int dfm_engine_replay(void* engine, int which, dfm_stream_t stream);
+/* One end-to-end step: async H2D of `host_slab` (pinned) on an internal copy stream, graph replay on
+ * `stream`, async D2H of the batch loss sum into `loss_host` (pinned, may be NULL). */
+int dfm_engine_step_from_host(void* engine, const void* host_slab, float* loss_host, dfm_stream_t stream);
 /* Device pointer + element count of an internal buffer:
  * "prob","logit","dlogit","fm_part","s_sum","state","dense_grad","dense_bf16","G","Gw",
  * "uniq_ids","slot_of", and "act"/"dz" with a layer index. */

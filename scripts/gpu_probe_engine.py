@@ -64,7 +64,12 @@ def run(B, layers, Ke=32, F=39, V=5000, opt="GD", lr=1.0, l2=0.0, mode="lazy", t
     st = eng.read_state()
     print("state after step:", st, "unique ref", ids.unique().numel())
     m.zero_grad()
-    loss = m.loss(m(ids, vals, training=False), labels)
+    def rt(x): return x + (x.bfloat16().float() - x).detach()
+    y_w, y_v, e = m.fm_terms(ids, vals)
+    h = rt(e.reshape(B, -1))
+    for l in range(len(layers)):
+        h = rt(torch.relu(h @ rt(m.mlp_w[l]) + m.mlp_b[l]))
+    loss = m.loss(m.fm_bias + y_w + y_v + (h @ m.out_w).view(-1) + m.out_b, labels)
     loss.backward()
     after = eng.variables()
     # dz buffers

@@ -29,6 +29,21 @@ def _setup(B, layers, Ke=32, F=39, V=5000, opt="GD", lr=1.0, l2=0.0, mode="lazy"
     return cfg, m, eng, ids, vals, labels
 
 
+def _rt(x):
+    """bf16 rounding with a straight-through gradient (what the tensor-core path sees)."""
+    return x + (x.bfloat16().float() - x).detach()
+
+
+def _emulated_logits(m, ids, vals):
+    """The oracle with the engine's rounding points: bf16 MLP inputs/weights/activations,
+    fp32 accumulation, fp32 FM terms and out layer."""
+    y_w, y_v, e = m.fm_terms(ids, vals)
+    h = _rt(e.reshape(e.shape[0], -1))
+    for l in range(len(m.cfg.deep_layers)):
+        h = _rt(torch.relu(h @ _rt(m.mlp_w[l]) + m.mlp_b[l]))
+    return m.fm_bias + y_w + y_v + (h @ m.out_w).view(-1) + m.out_b
+
+
 def _rel(a, b):
     return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
 
@@ -61,7 +76,7 @@ def test_gd_step_equals_autograd_gradients(B, layers, Ke, l2, mode):
     torch.cuda.synchronize()
     st = eng.read_state()
     assert st["step"] == 2 and st["n_unique"] == 0
-    m.loss(m(ids, vals), labels).backward()
+    m.loss(_emulated_logits(m, ids, vals), labels).backward()
     touched = torch.zeros(cfg.feature_size, dtype=torch.bool, device="cuda")
     touched[ids.unique()] = True
     for name, p in m.tf_variables().items():
@@ -69,7 +84,7 @@ def test_gd_step_equals_autograd_gradients(B, layers, Ke, l2, mode):
         ref = p.grad
         if name in ("fm_w", "fm_v") and mode == "lazy":
             ref = torch.where(touched if name == "fm_w" else touched[:, None], ref, torch.zeros_like(ref))
-        assert _rel(got, ref) < 3e-2, name
+        assert _rel(got, ref) < 2e-2, name
     # bookkeeping is clean for the next step
     assert eng.buffer("G").abs().max().item() == 0
     assert eng.buffer("dense_grad").abs().max().item() == 0
@@ -89,7 +104,7 @@ def test_optimizers_track_eager_reference(opt):
     for step in range(3):
         eng.train_step(ids32, vals, labels)
         m.zero_grad()
-        m.data_loss(m(ids, vals), labels).backward()
+        m.data_loss(_emulated_logits(m, ids, vals), labels).backward()
         with torch.no_grad():
             for name, p in m.trainable_tf_variables().items():
                 if name in ("fm_w", "fm_v"):       # lazy: touched rows, L2 on those rows
@@ -103,7 +118,7 @@ def test_optimizers_track_eager_reference(opt):
         got = eng.variables()[name]
         if name == "fm_v":
             got, p = got[uniq], p[uniq]
-        assert _rel(got, p) < 2e-2, (opt, name)
+        assert _rel(got, p) < 3e-2, (opt, name)
     eng.close()
 
 
