@@ -1,0 +1,280 @@
+// In-kernel collectives over NVLink / NVSwitch peer memory: no NCCL call on the training path.
+//
+// Every rank owns one "symmetric block" (same layout on all ranks) that its peers map through
+// CUDA IPC.  Kernels address peer memory directly with ld/st (P2P over NVLink 5); cross-GPU
+// ordering uses per-CTA flag words with release/acquire at system scope and a monotonically
+// increasing epoch kept in device memory, so the same code replays inside a CUDA graph.
+//
+//   dense_allreduce_opt_kernel   replaces Horovod's fused-buffer ncclAllReduce + ApplyAdam for the
+//       MLP / out-layer / fm_bias gradients (SURVEY X3 + K14): two-shot all-reduce (each rank
+//       reduces 1/N of the vector from all peers, writes the average back to all peers) fused with
+//       the 1/N scale, the optimizer update, the bf16 weight refresh and the gradient clear.
+//   sparse_push_claim_kernel +   replace Horovod's ncclAllGather of IndexedSlices + the sparse
+//   sparse_merge_apply_kernel    apply on the tables (SURVEY X4 + K13 + K14): every rank stores its
+//       de-duplicated (id, gradient row) list into each peer's inbox, the receivers merge the N
+//       lists by id in rank order (bit-identical on every replica), scale by 1/N and run the lazy
+//       optimizer on the union of touched rows.
+//
+// Deadlock safety: CTA i only ever waits for CTA i of the other ranks, and all ranks launch the same
+// grid in the same stream order; spins are bounded by a watchdog that traps instead of hanging.
+#include "engine.cuh"
+
+namespace dfm {
+
+constexpr int kCommThreads = 256;
+constexpr long long kCommWatchdog = 10000000000LL;   // ~5 s
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_volatile_f(const float* p) {
+  float v;
+  asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int ld_volatile_i(const int* p) {
+  int v;
+  asm volatile("ld.volatile.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Barrier among the CTAs with index blockIdx.x of all ranks.  `slot` selects one of the flag arrays.
+// Everything the calling CTA wrote before (to any GPU) is visible to its peers' matching CTA after.
+__device__ __forceinline__ void cta_barrier_all_ranks(const CommView& cv, int slot, unsigned int epoch) {
+  __threadfence_system();
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < cv.world) {
+    unsigned int* peer_flags = reinterpret_cast<unsigned int*>(cv.base[t] + cv.off_flags);
+    st_release_sys(peer_flags + (size_t(slot) * cv.world + cv.rank) * kCommMaxCtas + blockIdx.x, epoch);
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(cv.base[cv.rank] + cv.off_flags) +
+                               (size_t(slot) * cv.world + t) * kCommMaxCtas + blockIdx.x;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(mine) < epoch) {
+      if (clock64() - t0 > kCommWatchdog) {
+        printf("[dfm comm watchdog] rank %d cta %d slot %d waiting for rank %d epoch %u\n", cv.rank, blockIdx.x,
+               slot, t, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCommThreads)
+dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __restrict__ s0,
+                           float* __restrict__ s1, const float* __restrict__ part, int ksplit,
+                           size_t part_stride, __nv_bfloat16* __restrict__ Wb, int n,
+                           const StepState* __restrict__ st, const OptHyper hyper) {
+  const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
+  const unsigned int epoch = unsigned(st->comm_epoch) + 1u;
+  const int N = cv.world;
+  const float inv_n = 1.f / float(N);
+  const int n_red = n - 1;                            // element n-1 (fm_bias) shares the gradient of n-2
+  const int n4 = (n_red + 3) / 4;                     // float4 groups (buffers are padded)
+  const int shard4 = (n4 + N - 1) / N;                // groups per rank
+  const int sub4 = (shard4 + gridDim.x - 1) / gridDim.x;   // groups per (rank, CTA)
+
+  float* my_dP = reinterpret_cast<float*>(cv.base[cv.rank] + cv.off_dP);
+  float* my_avg = reinterpret_cast<float*>(cv.base[cv.rank] + cv.off_avg);
+
+  // local: add the split-K slices of the weight-gradient GEMM into the symmetric gradient buffer.
+  // CTA b sums exactly the groups that the peers' CTA b will read, so the per-CTA barrier below is enough.
+  for (int r = 0; r < N; ++r) {
+    const int g0 = r * shard4 + blockIdx.x * sub4;
+    const int g1 = min(min(g0 + sub4, (r + 1) * shard4), n4);
+    for (int g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < ksplit; ++k) {
+        const float4 v = *reinterpret_cast<const float4*>(part + size_t(k) * part_stride + 4 * size_t(g));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      *reinterpret_cast<float4*>(my_dP + 4 * size_t(g)) = acc;
+    }
+  }
+
+  // A: every rank's local gradients are complete -> safe to read them remotely
+  cta_barrier_all_ranks(cv, 0, epoch);
+
+  // reduce-scatter my shard, fused with the 1/N scale; all-gather by storing to every peer
+  {
+    const int g0 = cv.rank * shard4 + blockIdx.x * sub4;
+    const int g1 = min(min(g0 + sub4, (cv.rank + 1) * shard4), n4);
+    for (int g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < N; ++r) {
+        const float4 v = ld_volatile_f4(reinterpret_cast<const float*>(cv.base[r] + cv.off_dP) + 4 * size_t(g));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      acc.x *= inv_n; acc.y *= inv_n; acc.z *= inv_n; acc.w *= inv_n;
+      for (int r = 0; r < N; ++r)
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(cv.base[r] + cv.off_avg) + 4 * size_t(g)) = acc;
+    }
+  }
+
+  // B: the averaged slices written by CTA blockIdx.x of every rank have landed here, and every peer
+  //    has finished reading the matching slices of my gradient buffer
+  cta_barrier_all_ranks(cv, 1, epoch);
+
+  for (int r = 0; r < N; ++r) {
+    const int g0 = r * shard4 + blockIdx.x * sub4;
+    const int g1 = min(min(g0 + sub4, (r + 1) * shard4), n4);
+    for (int g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+      const float4 a4 = ld_volatile_f4(my_avg + 4 * size_t(g));
+      const float gr[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = 4 * g + j;
+        if (i >= n_red) break;
+        float p = P[i], a = s0[i], b = s1[i];
+        opt_apply(c, gr[j], p, a, b);
+        P[i] = p; s0[i] = a; s1[i] = b;
+        Wb[i] = __float2bfloat16(p);
+        if (i == n - 2) {
+          float p2 = P[n - 1], a2 = s0[n - 1], b2 = s1[n - 1];
+          opt_apply(c, gr[j], p2, a2, b2);
+          P[n - 1] = p2; s0[n - 1] = a2; s1[n - 1] = b2;
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Inbox layout inside the symmetric block, per sender rank r:
+//   count   int[world]                    at off_in_count
+//   ids     int  [world][cap]             at off_in_ids
+//   rows    float[world][cap][row_pitch]  at off_in_rows     row = Ke gradient values, then gw
+__global__ void __launch_bounds__(kCommThreads)
+sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict__ entry_of,
+                         int* __restrict__ touched, int* __restrict__ union_ids) {
+  const unsigned int epoch = unsigned(a.st->comm_epoch) + 1u;
+  const int N = cv.world, Ke = a.Ke, pitch = cv.row_pitch;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int warp_g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int n = a.st->n_unique;
+
+  // ---- push: my (id, row) list into inbox[cv.rank] of every rank (own included) ----
+  for (int s = warp_g; s < n; s += warps) {
+    const int id = a.uniq_ids[s];
+    for (int k = lane; k <= Ke; k += 32) {
+      float v;
+      if (k < Ke) { v = a.G[size_t(s) * Ke + k]; a.G[size_t(s) * Ke + k] = 0.f; }
+      else        { v = a.Gw[s]; a.Gw[s] = 0.f; }
+      for (int r = 0; r < N; ++r) {
+        float* rows = reinterpret_cast<float*>(cv.base[r] + cv.off_in_rows) + (size_t(cv.rank) * cv.cap + s) * pitch;
+        rows[k] = v;
+      }
+    }
+    if (lane == 0) {
+      for (int r = 0; r < N; ++r)
+        reinterpret_cast<int*>(cv.base[r] + cv.off_in_ids)[size_t(cv.rank) * cv.cap + s] = id;
+      a.slot_of[id] = -1;
+    }
+  }
+  if (threadIdx.x < N)
+    reinterpret_cast<int*>(cv.base[threadIdx.x] + cv.off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n;
+
+  cta_barrier_all_ranks(cv, 2, epoch);
+
+  // ---- claim: index every received entry by (id, sender) and build the union id list ----
+  const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_count);
+  const int* in_ids = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_ids);
+  for (int r = 0; r < N; ++r) {
+    const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
+    // the rows pushed by CTA blockIdx.x of rank r are exactly those this CTA's warps index
+    for (int s = warp_g; s < nr; s += warps) {
+      if (lane == 0) {
+        const int id = ld_volatile_i(in_ids + size_t(r) * cv.cap + s);
+        entry_of[size_t(id) * N + r] = s + 1;
+        if (atomicCAS(&touched[id], 0, 1) == 0) union_ids[atomicAdd(&a.st->n_union, 1)] = id;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kCommThreads)
+sparse_merge_apply_kernel(const CommView cv, const SparseArgs a, int* __restrict__ entry_of,
+                          int* __restrict__ touched, const int* __restrict__ union_ids, const OptHyper hyper) {
+  const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
+  const int N = cv.world, Ke = a.Ke, pitch = cv.row_pitch;
+  const float inv_n = 1.f / float(N);
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int n = a.st->n_union;
+  const float* in_rows = reinterpret_cast<const float*>(cv.base[cv.rank] + cv.off_in_rows);
+
+  for (int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; u < n; u += warps) {
+    const int id = union_ids[u];
+    int ent = 0;
+    if (lane < N) {
+      ent = entry_of[size_t(id) * N + lane];
+      entry_of[size_t(id) * N + lane] = 0;
+    }
+    int e_r[kCommMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kCommMaxRanks; ++r) e_r[r] = __shfl_sync(0xffffffffu, ent, r);   // 0 for r >= N
+    for (int k = lane; k <= Ke; k += 32) {
+      float acc = 0.f;
+#pragma unroll
+      for (int r = 0; r < kCommMaxRanks; ++r)            // rank order: identical sum on every replica
+        if (e_r[r]) acc += ld_volatile_f(in_rows + (size_t(r) * cv.cap + (e_r[r] - 1)) * pitch + k);
+      if (k < Ke) {
+        const size_t pi = size_t(id) * Ke + k;
+        float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
+        opt_apply(c, acc * inv_n + hyper.l2_reg * p, p, m, v);
+        a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
+      } else {
+        float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
+        opt_apply(c, acc * inv_n + hyper.l2_reg * p, p, m, v);
+        a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
+      }
+    }
+    if (lane == 0) touched[id] = 0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&a.st->sparse_done, 1) == int(gridDim.x) - 1) {
+      a.st->n_unique = 0;
+      a.st->n_union = 0;
+      a.st->sparse_done = 0;
+      a.st->step += 1;
+      a.st->comm_epoch += 1;
+      __threadfence();
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+int launch_dense_allreduce_opt(const CommView& cv, float* P, float* s0, float* s1, const float* part, int ksplit,
+                               size_t part_stride, __nv_bfloat16* Wb, int n, const StepState* st, const OptHyper& h,
+                               cudaStream_t stream) {
+  dense_allreduce_opt_kernel<<<cv.dense_ctas, kCommThreads, 0, stream>>>(cv, P, s0, s1, part, ksplit, part_stride,
+                                                                      Wb, n, st, h);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+int launch_sparse_exchange_apply(const CommView& cv, const SparseArgs& a, int* entry_of, int* touched, int* union_ids,
+                                 const OptHyper& h, cudaStream_t stream) {
+  sparse_push_claim_kernel<<<cv.sparse_ctas, kCommThreads, 0, stream>>>(cv, a, entry_of, touched, union_ids);
+  DFM_LAUNCH_CHECK();
+  sparse_merge_apply_kernel<<<cv.sparse_ctas, kCommThreads, 0, stream>>>(cv, a, entry_of, touched, union_ids, h);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+}  // namespace dfm

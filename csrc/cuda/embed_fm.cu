@@ -48,21 +48,14 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
       id_l = __ldg(my_ids + f0 + lane);
       x_l = __ldg(my_vals + f0 + lane);
       yw += __ldg(fm_w + id_l) * x_l;
-      if (dedupe) {
-        // claim a slot for this id if nobody has yet (-1 free, -2 being claimed, >=0 slot)
-        if (slot_of[id_l] == -1 && atomicCAS(&slot_of[id_l], -1, -2) == -1) {
-          const int s = atomicAdd(&st->n_unique, 1);
-          uniq_ids[s] = id_l;
-          slot_of[id_l] = s;
-        }
-      }
     }
-    // 4 fields in flight per iteration: independent 128 B row gathers
-    for (int f = 0; f < nf; f += 4) {
-      float row[4][KPL];
-      float xs[4];
+    // U fields in flight per iteration: independent 128 B row gathers (the kernel is latency-bound)
+    constexpr int U = KPL == 1 ? 8 : 4;
+    for (int f = 0; f < nf; f += U) {
+      float row[U][KPL];
+      float xs[U];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         const int ff = min(f + u, nf - 1);
         const int id = __shfl_sync(0xffffffffu, id_l, ff);
         xs[u] = __shfl_sync(0xffffffffu, x_l, ff);
@@ -74,7 +67,7 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         if (f + u < nf) {
           __nv_bfloat16* dst = e + size_t(b) * pitch + size_t(f0 + f + u) * Ke;
 #pragma unroll
@@ -105,6 +98,47 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
   if (lane == 0) fm_part[b] = tot + __ldg(fm_bias);
+}
+
+// Sparse-gradient bookkeeping, off the critical path (runs on the side stream while the forward pass
+// computes): every distinct id of the batch claims a compact slot.  One thread per (example, field).
+// Fields whose id is the same for every example (the numeric Criteo fields) would make the whole grid
+// CAS one slot_of entry; a thread that sees the CTA's first example carry the same id in the same
+// field leaves the claim to that thread, so such an id costs one CAS per CTA.
+__global__ void __launch_bounds__(1024)
+dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, int* __restrict__ slot_of,
+              int* __restrict__ uniq_ids) {
+  const int total = st->count * F;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  int won = 0, id = 0;
+  if (i < total) {
+    id = __ldg(ids + i);
+    // reference example: the first one that starts inside this CTA's range of pairs
+    const int first = blockIdx.x * blockDim.x;
+    const int ref = ((first + F - 1) / F) * F + (i % F);
+    const bool leave = ref != i && ref < first + int(blockDim.x) && ref < total && __ldg(ids + ref) == id;
+    if (!leave && slot_of[id] == -1 && atomicCAS(&slot_of[id], -1, -2) == -1) won = 1;
+  }
+  const unsigned winners = __ballot_sync(0xffffffffu, won);
+  if (winners) {
+    const int leader = __ffs(winners) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(&st->n_unique, __popc(winners));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (won) {
+      const int s = base + __popc(winners & ((1u << lane) - 1u));
+      uniq_ids[s] = id;
+      slot_of[id] = s;
+    }
+  }
+}
+
+int launch_dedupe(const int* ids, int F, StepState* st, int* slot_of, int* uniq_ids, int batch_max,
+                  cudaStream_t stream) {
+  dedupe_kernel<<<ceil_div(batch_max * F, 1024), 1024, 0, stream>>>(ids, F, st, slot_of, uniq_ids);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
 }
 
 // Writes the constant ones column (and zeroes the pad) of an activation buffer.

@@ -37,13 +37,13 @@ struct Engine {
   StepState* st = nullptr;
   WgradItem* items = nullptr;
   int n_items = 0;
+  int ksplit = 1;
+  size_t part_stride = 0;      // dP holds [ksplit][part_stride] split-K slices of the dense gradient
 
-  FwdMaps fmaps; BwdMaps bmaps; WgradMaps wmaps;
-  int fwd_smem = 0, fwd_stages = 0, fwd_bslot = 0, fwd_chunks = 0;
-  int bwd_smem = 0, bwd_stages = 0, bwd_bslot = 0, bwd_chunks = 0;
+  FwdMaps fmaps; WgradMaps wmaps;
 
   cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork0 = nullptr;
 
   // optional: the captured train step and the double-buffered host->device input pipeline
   static constexpr int kPipe = 2;
@@ -53,6 +53,14 @@ struct Engine {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[kPipe] = {nullptr, nullptr}, ev_done[kPipe] = {nullptr, nullptr};
   long long pipe_step = 0;
+
+  // multi-GPU: symmetric block + peer mappings (see comm.cu)
+  CommView cv{};
+  uint8_t* symm = nullptr;
+  size_t symm_bytes = 0;
+  bool comm_ready = false;
+  int *entry_of = nullptr, *touched = nullptr, *union_ids = nullptr;
+  std::vector<void*> peer_maps;
 
   template <typename T>
   int alloc(T** p, size_t n, int fill_byte = 0) {
@@ -102,7 +110,6 @@ static int engine_build(Engine& E) {
   int rc;
   const size_t rows = E.Bpad;
   if ((rc = E.alloc(&E.Wb, size_t(E.n_dense) + 8))) return rc;
-  if ((rc = E.alloc(&E.dP, size_t(E.n_dense) + 8))) return rc;
   for (int l = 0; l <= sh.L; ++l) {
     if ((rc = E.alloc(&E.act[l], rows * sh.pitch[l]))) return rc;
     if ((rc = launch_fill_ones_column(E.act[l], int(rows), sh.pitch[l], sh.K[l], nullptr))) return rc;
@@ -121,24 +128,18 @@ static int engine_build(Engine& E) {
   if ((rc = E.alloc(&E.slot_of, size_t(c.feature_size), 0xFF))) return rc;   // all -1
   if ((rc = E.alloc(&E.st, 1))) return rc;
 
-  // ---- shared-memory plans ----
-  E.fwd_smem = mlp_fwd_plan(sh, &E.fwd_stages, &E.fwd_bslot, &E.fwd_chunks);
-  DFM_REQUIRE(E.fwd_smem > 0, "deep_layers too wide for the fused forward kernel's shared-memory plan");
-  E.bwd_smem = mlp_bwd_plan(sh, &E.bwd_stages, &E.bwd_bslot, &E.bwd_chunks);
-  DFM_REQUIRE(E.bwd_smem > 0, "deep_layers too wide for the fused backward kernel's shared-memory plan");
-  if ((rc = mlp_fwd_set_smem(E.fwd_smem))) return rc;
-  if ((rc = mlp_bwd_set_smem(E.bwd_smem))) return rc;
+  // ---- kernel attributes ----
+  if ((rc = mlp_layer_set_smem())) return rc;
+  if ((rc = embed_bwd_set_smem())) return rc;
   if ((rc = wgrad_set_smem())) return rc;
 
   // ---- TMA descriptors ----
-  if ((rc = make_tmap_bf16_2d(&E.fmaps.e, E.act[0], sh.K[0], rows, size_t(sh.pitch[0]) * 2, 64, kTileM))) return rc;
   for (int l = 0; l < sh.L; ++l) {
     const __nv_bfloat16* w = E.Wb + E.off[l];
+    if ((rc = make_tmap_bf16_2d(&E.fmaps.act[l], E.act[l], sh.K[l], rows, size_t(sh.pitch[l]) * 2, 64, kTileM))) return rc;
     if ((rc = make_tmap_bf16_2d(&E.fmaps.w[l], w, sh.N[l], sh.K[l], size_t(sh.N[l]) * 2, 64, 64))) return rc;
-    if ((rc = make_tmap_bf16_2d(&E.bmaps.w[l], w, sh.N[l], sh.K[l], size_t(sh.N[l]) * 2, 64, std::min(256, sh.K[l]))))
-      return rc;
+    if ((rc = make_tmap_bf16_2d(&E.fmaps.dz[l], E.dz[l], sh.N[l], rows, size_t(sh.N[l]) * 2, 64, kTileM))) return rc;
   }
-  if ((rc = make_tmap_bf16_2d(&E.bmaps.dz0, E.dz[0], sh.N[0], rows, size_t(sh.N[0]) * 2, 64, kTileM))) return rc;
   for (int l = 0; l <= sh.L; ++l) {
     if ((rc = make_tmap_bf16_2d(&E.wmaps.act[l], E.act[l], sh.K[l] + 1, rows, size_t(sh.pitch[l]) * 2, 64, 64))) return rc;
     const int ncol = l < sh.L ? sh.N[l] : 16;
@@ -151,7 +152,7 @@ static int engine_build(Engine& E) {
     const int ncol = l < sh.L ? sh.N[l] : 16;
     for (int m0 = 0; m0 < sh.K[l] + 1; m0 += kTileM)
       for (int n0 = 0; n0 < ncol; n0 += 256)
-        base.push_back(WgradItem{l, m0, n0, std::min(256, round_up(ncol - n0, 16)), 0, 0});
+        base.push_back(WgradItem{l, m0, n0, std::min(256, round_up(ncol - n0, 16)), 0, 0, 0});
   }
   const int k_chunks = ceil_div(int(rows), kChunkK);
   int ksplit = std::max(1, std::min(k_chunks, 148 / std::max<int>(1, int(base.size()))));
@@ -162,8 +163,12 @@ static int engine_build(Engine& E) {
     for (auto it : base) {
       it.k_begin = s * per * kChunkK;
       it.k_end = std::min(k_chunks, (s + 1) * per) * kChunkK;
+      it.ks = s;
       items.push_back(it);
     }
+  E.ksplit = ksplit;
+  E.part_stride = size_t(round_up(E.n_dense, 4)) + 8;
+  if ((rc = E.alloc(&E.dP, E.part_stride * ksplit))) return rc;
   E.n_items = int(items.size());
   if ((rc = E.alloc(&E.items, items.size()))) return rc;
   DFM_CUDA_CHECK(cudaMemcpy(E.items, items.data(), items.size() * sizeof(WgradItem), cudaMemcpyHostToDevice));
@@ -171,6 +176,7 @@ static int engine_build(Engine& E) {
   DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&E.side, cudaStreamNonBlocking));
   DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_fork, cudaEventDisableTiming));
   DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_join, cudaEventDisableTiming));
+  DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_fork0, cudaEventDisableTiming));
 
   StepState init{};
   init.count = c.batch_max; init.step = 1; init.lr = c.lr; init.train = 1;
@@ -180,24 +186,36 @@ static int engine_build(Engine& E) {
   return DFM_OK;
 }
 
-static int engine_forward(Engine& E, const int* ids, const float* vals, const float* labels, int dedupe,
+static int engine_forward(Engine& E, const int* ids, const float* vals, const float* labels, int train,
                           cudaStream_t s) {
   const dfm_engine_config& c = E.cfg;
-  const float* fm_bias = E.t.dense + E.off[E.sh.L + 1];
-  int rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], E.sh.pitch[0], E.s_sum, E.fm_part,
-                               c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, dedupe, s);
-  if (rc) return rc;
-  FwdParams fp{};
-  fp.sh = E.sh;
-  for (int l = 0; l <= E.sh.L; ++l) {
-    fp.P[l] = E.t.dense + E.off[l];
-    fp.act[l] = E.act[l];
+  const MlpShape& sh = E.sh;
+  int rc;
+  if (train) {
+    // sparse-gradient bookkeeping runs beside the forward pass; its results are first needed by embed_bwd,
+    // which is queued behind it on the same side stream
+    DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
+    if ((rc = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side))) return rc;
   }
-  fp.fm_part = E.fm_part; fp.labels = labels; fp.logit = E.logit; fp.prob = E.prob;
-  fp.dlogit = dedupe ? E.dlogit : nullptr;
-  fp.st = E.st; fp.seed = c.seed; fp.stages = E.fwd_stages; fp.b_slot_bytes = E.fwd_bslot;
-  fp.a_region_chunks = E.fwd_chunks;
-  return launch_mlp_fwd(E.fmaps, fp, c.batch_max, E.fwd_smem, s);
+  const float* fm_bias = E.t.dense + E.off[sh.L + 1];
+  if ((rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], sh.pitch[0], E.s_sum, E.fm_part,
+                                c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, 0, s)))
+    return rc;
+  for (int l = 0; l < sh.L; ++l) {
+    LayerParams lp{};
+    lp.st = E.st; lp.bias = E.t.dense + E.off[l] + size_t(sh.K[l]) * sh.N[l];
+    lp.out = E.act[l + 1]; lp.out_pitch = sh.pitch[l + 1];
+    lp.n_out = sh.N[l]; lp.k_red = sh.K[l]; lp.b_box_rows = 64; lp.layer = l; lp.keep = sh.keep[l]; lp.seed = c.seed;
+    if ((rc = launch_mlp_layer(false, E.fmaps.act[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
+  }
+  LossParams q{};
+  q.st = E.st; q.h_last = E.act[sh.L]; q.h_pitch = sh.pitch[sh.L]; q.n_last = sh.K[sh.L];
+  q.w_out = E.t.dense + E.off[sh.L]; q.fm_part = E.fm_part; q.labels = labels;
+  q.logit = E.logit; q.prob = E.prob; q.dlogit = train ? E.dlogit : nullptr;
+  q.dz_last = train ? E.dz[sh.L - 1] : nullptr; q.dz_out = E.dz[sh.L];
+  q.keep_last = sh.keep[sh.L - 1]; q.rows_pad = E.Bpad;
+  return launch_loss_init(q, train ? E.Bpad : c.batch_max, s);
 }
 
 static int engine_backward_update(Engine& E, const int* ids, const float* vals, cudaStream_t s) {
@@ -209,27 +227,39 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
     bp.dz[l] = E.dz[l];
   }
   bp.w_out = E.t.dense + E.off[E.sh.L];
-  bp.dlogit = E.dlogit; bp.st = E.st; bp.stages = E.bwd_stages; bp.b_slot_bytes = E.bwd_bslot;
-  bp.a_region_chunks = E.bwd_chunks;
+  bp.dlogit = E.dlogit; bp.st = E.st;
   bp.ids = ids; bp.vals = vals; bp.s_sum = E.s_sum; bp.slot_of = E.slot_of; bp.G = E.G; bp.Gw = E.Gw;
   bp.F = c.field_size; bp.Ke = c.embedding_size;
-  int rc = launch_mlp_bwd_chain(E.bmaps, bp, c.batch_max, E.bwd_smem, s);
-  if (rc) return rc;
+  int rc;
+  for (int l = E.sh.L - 1; l >= 1; --l) {       // dz_{l-1} = (h_l > 0) * (dz_l W_l^T) / keep_{l-1}
+    LayerParams lp{};
+    lp.st = E.st; lp.mask = E.act[l]; lp.mask_pitch = E.sh.pitch[l];
+    lp.out = E.dz[l - 1]; lp.out_pitch = E.sh.N[l - 1];
+    lp.n_out = E.sh.K[l]; lp.k_red = E.sh.N[l]; lp.b_box_rows = 64; lp.layer = l; lp.keep = E.sh.keep[l - 1];
+    lp.seed = c.seed;
+    if ((rc = launch_mlp_layer(true, E.fmaps.dz[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
+  }
 
   // fork: embedding gradient on the side stream, weight gradients + dense update on the main one
   DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork, s));
   DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork, 0));
-  if ((rc = launch_embed_bwd(E.bmaps, bp, c.batch_max, E.side))) return rc;
+  if ((rc = launch_embed_bwd(E.fmaps, bp, c.batch_max, E.side))) return rc;
   DFM_CUDA_CHECK(cudaEventRecord(E.ev_join, E.side));
 
   WgradParams wp{};
   wp.sh = E.sh;
   for (int l = 0; l <= E.sh.L; ++l) wp.dP[l] = E.dP + E.off[l];
-  wp.items = E.items; wp.st = E.st;
+  wp.items = E.items; wp.st = E.st; wp.part_stride = E.part_stride;
   if ((rc = launch_wgrad(E.wmaps, wp, E.n_items, s))) return rc;
   const float gscale = 1.f;
-  if ((rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.Wb, E.n_dense, E.st, E.hyper, gscale, s)))
+  if (E.comm_ready) {
+    if ((rc = launch_dense_allreduce_opt(E.cv, E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride,
+                                         E.Wb, E.n_dense, E.st, E.hyper, s)))
+      return rc;
+  } else if ((rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride, E.Wb,
+                                    E.n_dense, E.st, E.hyper, gscale, s))) {
     return rc;
+  }
 
   DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
   SparseArgs sa{};
@@ -237,6 +267,8 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   sa.fm_w = E.t.fm_w; sa.w_s0 = E.t.fm_w_s0; sa.w_s1 = E.t.fm_w_s1;
   sa.G = E.G; sa.Gw = E.Gw; sa.slot_of = E.slot_of; sa.uniq_ids = E.uniq_ids; sa.st = E.st;
   sa.Ke = c.embedding_size; sa.V = c.feature_size; sa.grad_scale = gscale;
+  if (E.comm_ready)
+    return launch_sparse_exchange_apply(E.cv, sa, E.entry_of, E.touched, E.union_ids, E.hyper, s);
   return launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
 }
 
@@ -263,10 +295,12 @@ extern "C" int dfm_engine_destroy(void* h) {
   if (!h) return DFM_OK;
   Engine* E = static_cast<Engine*>(h);
   cudaDeviceSynchronize();
+  for (void* p : E->peer_maps) cudaIpcCloseMemHandle(p);
   for (void* p : E->allocs) cudaFree(p);
   if (E->side) cudaStreamDestroy(E->side);
   if (E->ev_fork) cudaEventDestroy(E->ev_fork);
   if (E->ev_join) cudaEventDestroy(E->ev_join);
+  if (E->ev_fork0) cudaEventDestroy(E->ev_fork0);
   for (int i = 0; i < Engine::kPipe; ++i) {
     if (E->graph[i]) cudaGraphExecDestroy(E->graph[i]);
     if (E->ev_h2d[i]) cudaEventDestroy(E->ev_h2d[i]);
@@ -302,7 +336,103 @@ extern "C" int dfm_engine_train_step(void* h, const int* ids, const float* vals,
   return engine_backward_update(*E, ids, vals, s);
 }
 
-extern "C" int dfm_engine_launches_per_step(void* h) { (void)h; return 7; }
+extern "C" int dfm_engine_launches_per_step(void* h) {
+  Engine* E = static_cast<Engine*>(h);
+  // dedupe, embed_fwd, L forward layers, loss, L-1 backward layers, embed_bwd, wgrad, dense opt, sparse (1 or 2)
+  return 2 + E->sh.L + 1 + (E->sh.L - 1) + 3 + (E->comm_ready ? 2 : 1);
+}
+
+// ---- phase timing (warm, CUDA events) ----------------------------------------------------------
+// ms_out[0] = forward (dedupe beside embed+FM, MLP layers, loss), ms_out[1] = backward + update,
+// ms_out[2] = whole step.  Means over `iters` real training steps.  Single-GPU only.
+extern "C" int dfm_engine_profile(void* h, const int* ids, const float* vals, const float* labels, int iters,
+                                  float* ms_out) {
+  Engine& E = *static_cast<Engine*>(h);
+  DFM_REQUIRE(!E.comm_ready, "dfm_engine_profile is single-GPU only");
+  cudaStream_t s = nullptr;
+  DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  cudaEvent_t ev[3];
+  for (auto& e : ev) DFM_CUDA_CHECK(cudaEventCreate(&e));
+  for (int i = 0; i < 3; ++i) ms_out[i] = 0.f;
+  int rc = DFM_OK;
+  for (int it = -3; it < iters && !rc; ++it) {
+    cudaEventRecord(ev[0], s);
+    rc = engine_forward(E, ids, vals, labels, 1, s);
+    cudaEventRecord(ev[1], s);
+    if (!rc) rc = engine_backward_update(E, ids, vals, s);
+    cudaEventRecord(ev[2], s);
+    DFM_CUDA_CHECK(cudaStreamSynchronize(s));
+    if (it >= 0) {
+      float a = 0.f, b = 0.f;
+      cudaEventElapsedTime(&a, ev[0], ev[1]);
+      cudaEventElapsedTime(&b, ev[1], ev[2]);
+      ms_out[0] += a / iters; ms_out[1] += b / iters; ms_out[2] += (a + b) / iters;
+    }
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  cudaStreamDestroy(s);
+  return rc;
+}
+
+// ---- multi-GPU attachment ---------------------------------------------------------------------
+// Step 1 (every rank): allocate the symmetric block and export it.
+extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_handle_out /* 64 bytes */) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(world >= 2 && world <= kCommMaxRanks && rank >= 0 && rank < world, "comm: world %d rank %d unsupported",
+              world, rank);
+  DFM_REQUIRE(E->cfg.table_update_mode == DFM_TABLE_LAZY, "multi-GPU fused path implements the lazy table update");
+  DFM_REQUIRE(!E->symm, "comm already allocated");
+  CommView& cv = E->cv;
+  cv.world = world; cv.rank = rank;
+  cv.cap = E->cfg.batch_max * E->cfg.field_size;
+  cv.row_pitch = round_up(E->cfg.embedding_size + 1, 4);
+  cv.dense_ctas = 64;
+  cv.sparse_ctas = 148;
+  auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
+  size_t o = 0;
+  const size_t n4 = size_t(round_up(E->n_dense, 4)) + 8;
+  cv.off_dP = o;        o = align(o + n4 * 4);
+  cv.off_avg = o;       o = align(o + n4 * 4);
+  cv.off_flags = o;     o = align(o + size_t(3) * world * kCommMaxCtas * 4);
+  cv.off_in_count = o;  o = align(o + size_t(world) * kCommMaxCtas * 4);
+  cv.off_in_ids = o;    o = align(o + size_t(world) * cv.cap * 4);
+  cv.off_in_rows = o;   o = align(o + size_t(world) * cv.cap * cv.row_pitch * 4);
+  E->symm_bytes = o;
+  void* p = nullptr;
+  DFM_CUDA_CHECK(cudaMalloc(&p, o));
+  DFM_CUDA_CHECK(cudaMemset(p, 0, o));
+  E->allocs.push_back(p);
+  E->symm = static_cast<uint8_t*>(p);
+  cudaIpcMemHandle_t hd;
+  DFM_CUDA_CHECK(cudaIpcGetMemHandle(&hd, p));
+  static_assert(sizeof(hd) == 64, "IPC handle size");
+  memcpy(ipc_handle_out, &hd, 64);
+  int rc;
+  if ((rc = E->alloc(&E->entry_of, size_t(E->cfg.feature_size) * world))) return rc;
+  if ((rc = E->alloc(&E->touched, size_t(E->cfg.feature_size)))) return rc;
+  if ((rc = E->alloc(&E->union_ids, size_t(cv.cap) * world))) return rc;
+  DFM_CUDA_CHECK(cudaDeviceSynchronize());
+  return DFM_OK;
+}
+
+// Step 2 (every rank, after an all-gather of the handles): map the peers and switch the step to the
+// in-kernel collectives.  The local gradient buffer moves into the symmetric block.
+extern "C" int dfm_engine_comm_attach(void* h, const void* all_handles /* world x 64 bytes */) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(E->symm, "call dfm_engine_comm_alloc first");
+  CommView& cv = E->cv;
+  for (int r = 0; r < cv.world; ++r) {
+    if (r == cv.rank) { cv.base[r] = E->symm; continue; }
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, static_cast<const uint8_t*>(all_handles) + 64 * r, 64);
+    void* p = nullptr;
+    DFM_CUDA_CHECK(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+    E->peer_maps.push_back(p);
+    cv.base[r] = static_cast<uint8_t*>(p);
+  }
+  E->comm_ready = true;
+  return DFM_OK;
+}
 
 // ---- CUDA-graph replay + double-buffered input pipeline -------------------------------------
 // Input slab layout (host and device): ids int32 [batch_max*F] | vals f32 [batch_max*F] | labels f32 [batch_max]
@@ -402,7 +532,7 @@ extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** pt
   else if (!strcmp(name, "fm_part")) { p = E->fm_part; n = rows; }
   else if (!strcmp(name, "s_sum")) { p = E->s_sum; n = rows * E->cfg.embedding_size; }
   else if (!strcmp(name, "state")) { p = E->st; n = sizeof(StepState) / 4; }
-  else if (!strcmp(name, "dense_grad")) { p = E->dP; n = E->n_dense; }
+  else if (!strcmp(name, "dense_grad")) { p = E->dP; n = (long long)E->part_stride * E->ksplit; }
   else if (!strcmp(name, "dense_bf16")) { p = E->Wb; n = E->n_dense; }
   else if (!strcmp(name, "G")) { p = E->G; n = (long long)E->cfg.batch_max * E->cfg.field_size * E->cfg.embedding_size; }
   else if (!strcmp(name, "Gw")) { p = E->Gw; n = (long long)E->cfg.batch_max * E->cfg.field_size; }

@@ -29,7 +29,9 @@ struct StepState {
   int n_unique;       // distinct table rows touched by the current batch
   int sparse_done;    // CTAs of the sparse-apply kernel that have finished (last one resets)
   int train;          // 1: dropout active, gradients produced
-  int pad;
+  int n_union;        // multi-GPU: distinct rows touched by any rank this step
+  int comm_epoch;     // multi-GPU: completed collective rounds (flag value of the next round = +1)
+  int pad[3];
 };
 
 struct OptHyper {
@@ -112,29 +114,10 @@ __device__ __forceinline__ void opt_apply(const OptStepConsts& c, float g, float
 // Kernel parameter blocks (passed as __grid_constant__) and launchers
 // ---------------------------------------------------------------------------
 struct FwdMaps {
-  CUtensorMap e;                  // act[0] as [B, K0], box {64, 128}
+  CUtensorMap act[kMaxLayers];    // act[l] as [B, K_l], box {64, 128}   (A operand, forward)
   CUtensorMap w[kMaxLayers];      // Wb[l] as [K_l, N_l] (N contiguous), box {64, 64}
-};
-
-struct FwdParams {
-  MlpShape sh;
-  const float* P[kMaxLayers + 1];        // fp32 masters (bias rows, out layer)
-  __nv_bfloat16* act[kMaxLayers + 1];    // act[l+1] is written here
-  const float* fm_part;
-  const float* labels;                   // may be null (pure inference)
-  float* logit;
-  float* prob;
-  float* dlogit;
-  StepState* st;
-  unsigned long long seed;
-  int stages;
-  int b_slot_bytes;
-  int a_region_chunks;
-};
-
-struct BwdMaps {
-  CUtensorMap w[kMaxLayers];   // Wb[l] as [K_l rows, N_l cols], box {64, min(256, K_l)}  (K-major B)
-  CUtensorMap dz0;             // dz[0] as [B, N_0], box {64, 128}                         (K-major A)
+                                  //   forward: one MN-major atom at (n0, k0); backward: K-major rows at (k0, n0)
+  CUtensorMap dz[kMaxLayers];     // dz[l] as [B, N_l], box {64, 128}    (A operand, backward)
 };
 
 struct BwdParams {
@@ -164,6 +147,7 @@ struct WgradItem {
   int n_here;     // columns (multiple of 16, <= 256)
   int k_begin;    // batch range [k_begin, k_end), multiples of 64
   int k_end;
+  int ks;         // split-K slice this CTA writes
 };
 
 struct WgradMaps {
@@ -173,7 +157,8 @@ struct WgradMaps {
 
 struct WgradParams {
   MlpShape sh;
-  float* dP[kMaxLayers + 1];
+  float* dP[kMaxLayers + 1];     // layer bases inside slice 0 of the partial buffer
+  size_t part_stride;            // elements between split-K slices
   const WgradItem* items;
   StepState* st;
 };
@@ -189,22 +174,63 @@ struct SparseArgs {
   float grad_scale;
 };
 
+// One MLP layer launch (mlp_layer.cu)
+struct LayerParams {
+  StepState* st;
+  const float* bias;              // forward: b_l [N_l]
+  const __nv_bfloat16* mask;      // backward: h_l (input of layer l), row pitch mask_pitch
+  __nv_bfloat16* out;             // forward: h_{l+1} ; backward: dz_{l-1}
+  int out_pitch, mask_pitch;
+  int n_out;                      // output columns (N_l forward, K_l backward)
+  int k_red;                      // reduction length (K_l forward, N_l backward)
+  int b_box_rows;                 // rows of the B operand's TMA box (64)
+  int layer;
+  float keep;                     // forward: keep_l ; backward: keep_{l-1}
+  unsigned long long seed;
+};
+
+struct LossParams {
+  StepState* st;
+  const __nv_bfloat16* h_last; int h_pitch; int n_last;
+  const float* w_out;             // P_out: [n_last] weights then b_out
+  const float* fm_part; const float* labels;
+  float* logit; float* prob; float* dlogit;
+  __nv_bfloat16* dz_last;         // [rows, n_last] or null (inference)
+  __nv_bfloat16* dz_out;          // [rows, 16]
+  float keep_last;
+  int rows_pad;
+};
+
+// Multi-GPU view of the symmetric blocks (one per rank, identical layout, peers mapped via CUDA IPC).
+constexpr int kCommMaxRanks = 8;
+constexpr int kCommMaxCtas = 160;
+struct CommView {
+  uint8_t* base[kCommMaxRanks];
+  int world, rank;
+  int cap;            // inbox rows per sender (= batch_max * field_size)
+  int row_pitch;      // floats per inbox row (Ke + 1 rounded up to 4)
+  int dense_ctas, sparse_ctas;
+  size_t off_dP, off_avg, off_flags, off_in_count, off_in_ids, off_in_rows;
+};
+
 // launchers (one per translation unit)
+int launch_dense_allreduce_opt(const CommView&, float*, float*, float*, const float*, int, size_t,
+                               __nv_bfloat16*, int, const StepState*, const OptHyper&, cudaStream_t);
+int launch_sparse_exchange_apply(const CommView&, const SparseArgs&, int*, int*, int*, const OptHyper&, cudaStream_t);
 int launch_embed_fm_fwd(const int*, const float*, const float*, const float*, const float*, __nv_bfloat16*, int,
                         float*, float*, int, int, int, StepState*, int*, int*, int, cudaStream_t);
 int launch_fill_ones_column(__nv_bfloat16*, int, int, int, cudaStream_t);
-int mlp_fwd_plan(const MlpShape&, int*, int*, int*);
-int mlp_fwd_set_smem(int);
-int launch_mlp_fwd(const FwdMaps&, const FwdParams&, int, int, cudaStream_t);
-int mlp_bwd_plan(const MlpShape&, int*, int*, int*);
-int mlp_bwd_set_smem(int);
-int launch_mlp_bwd_chain(const BwdMaps&, const BwdParams&, int, int, cudaStream_t);
-int launch_embed_bwd(const BwdMaps&, const BwdParams&, int, cudaStream_t);
+int launch_dedupe(const int*, int, StepState*, int*, int*, int, cudaStream_t);
+int mlp_layer_set_smem();
+int launch_mlp_layer(bool, const CUtensorMap&, const CUtensorMap&, const LayerParams&, int, cudaStream_t);
+int launch_loss_init(const LossParams&, int, cudaStream_t);
+int embed_bwd_set_smem();
+int launch_embed_bwd(const FwdMaps&, const BwdParams&, int, cudaStream_t);
 int wgrad_set_smem();
 int launch_wgrad(const WgradMaps&, const WgradParams&, int, cudaStream_t);
 int launch_set_state(StepState*, int, float, int, int, cudaStream_t);
-int launch_dense_opt(float*, float*, float*, float*, __nv_bfloat16*, int, const StepState*, const OptHyper&, float,
-                     cudaStream_t);
+int launch_dense_opt(float*, float*, float*, const float*, int, size_t, __nv_bfloat16*, int, const StepState*,
+                     const OptHyper&, float, cudaStream_t);
 int launch_cast_weights(const float*, __nv_bfloat16*, int, cudaStream_t);
 int launch_sparse_apply(const SparseArgs&, const OptHyper&, int, bool, cudaStream_t);
 

@@ -24,12 +24,14 @@ __global__ void set_state_kernel(StepState* st, int count, float lr, int train, 
 // b_out (element n-2): y = fm_bias + ... + b_out.
 __global__ void __launch_bounds__(256)
 dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restrict__ s1,
-                 float* __restrict__ grad, __nv_bfloat16* __restrict__ Wb, int n,
+                 const float* __restrict__ part, int ksplit, size_t part_stride,
+                 __nv_bfloat16* __restrict__ Wb, int n,
                  const StepState* __restrict__ st, const OptHyper hyper, float grad_scale) {
   const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
-    const float g = grad[i] * grad_scale;
-    grad[i] = 0.f;
+    float g = 0.f;
+    for (int k = 0; k < ksplit; ++k) g += __ldg(part + size_t(k) * part_stride + i);   // fixed order
+    g *= grad_scale;
     float p = P[i], a = s0[i], b = s1[i];
     opt_apply(c, g, p, a, b);
     P[i] = p; s0[i] = a; s1[i] = b;
@@ -169,10 +171,11 @@ int launch_set_state(StepState* st, int count, float lr, int train, int step, cu
   return DFM_OK;
 }
 
-int launch_dense_opt(float* P, float* s0, float* s1, float* grad, __nv_bfloat16* Wb, int n, const StepState* st,
-                     const OptHyper& h, float grad_scale, cudaStream_t stream) {
-  const int grid = std::min(148 * 4, ceil_div(n, 256));
-  dense_opt_kernel<<<grid, 256, 0, stream>>>(P, s0, s1, grad, Wb, n, st, h, grad_scale);
+int launch_dense_opt(float* P, float* s0, float* s1, const float* part, int ksplit, size_t part_stride,
+                     __nv_bfloat16* Wb, int n, const StepState* st, const OptHyper& h, float grad_scale,
+                     cudaStream_t stream) {
+  const int grid = std::min(148 * 8, ceil_div(n, 256));
+  dense_opt_kernel<<<grid, 256, 0, stream>>>(P, s0, s1, part, ksplit, part_stride, Wb, n, st, h, grad_scale);
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }
@@ -189,7 +192,7 @@ int launch_sparse_apply(const SparseArgs& a, const OptHyper& h, int max_rows, bo
     const int grid = int(std::min<long long>(148 * 8, (warps_needed + 7) / 8));
     table_dense_kernel<<<grid, 256, 0, stream>>>(a, h);
   } else {
-    const int grid = std::max(1, std::min(148 * 4, ceil_div(max_rows, 8)));
+    const int grid = std::max(1, std::min(148 * 8, ceil_div(max_rows, 8)));
     sparse_apply_kernel<<<grid, 256, 0, stream>>>(a, h);
   }
   DFM_LAUNCH_CHECK();

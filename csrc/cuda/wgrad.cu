@@ -6,8 +6,9 @@
 // Both operands are used exactly as the forward/backward kernels left them in global memory
 // (row-major [batch, features]); with the batch as the GEMM K dimension that makes them
 // MN-major UMMA operands, so no transposed copies exist anywhere.  The batch is split across
-// CTAs (split-K) so the launch fills the chip; partial tiles are combined with fp32
-// red.global.add into the gradient buffer, which is the buffer the gradient all-reduce reads.
+// CTAs (split-K) so the launch fills the chip; every split writes its partial tile with plain
+// vector stores into its own slice of the partial buffer [ksplit][n_dense] (no atomics, no
+// zero-fill pass, deterministic), and the optimizer kernel adds the slices when it reads them.
 // Replaces the dW GEMMs + BiasAddGrad of TF autodiff for HVD.py:224-243.
 #include "engine.cuh"
 #include "ptx.cuh"
@@ -32,9 +33,19 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int count = p.st->count;
   const int k_lim = min(item.k_end, (count + 63) & ~63);
-  if (item.k_begin >= k_lim) return;
-  const int num_kc = (k_lim - item.k_begin) / kChunkK;
   const int l = item.layer;
+  if (item.k_begin >= k_lim) {
+    // this batch range is empty (short batch): the slice still has to read as zero
+    const int Nl = p.sh.N[l];
+    float* base = p.dP[l] + size_t(item.ks) * p.part_stride;
+    for (int r = threadIdx.x; r < kTileM; r += blockDim.x) {
+      const int r_out = item.m0 + r;
+      if (r_out >= p.sh.K[l] + 1) break;
+      for (int c = item.n0; c < min(Nl, item.n0 + item.n_here); ++c) base[size_t(r_out) * Nl + c] = 0.f;
+    }
+    return;
+  }
+  const int num_kc = (k_lim - item.k_begin) / kChunkK;
   const int b_atoms = (item.n_here + 63) / 64;
 
   if (warp == 0 && lane == 0) {
@@ -90,7 +101,7 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
     const int r_out = item.m0 + q * 32 + lane;        // row of dP_l
     const int Nl = p.sh.N[l];
     const bool row_ok = r_out < p.sh.K[l] + 1;
-    float* dst_row = p.dP[l] + size_t(r_out) * Nl;
+    float* dst_row = p.dP[l] + size_t(item.ks) * p.part_stride + size_t(r_out) * Nl;
     const uint32_t t_row = tmem_base + (uint32_t(q * 32) << 16);
     mbar_wait(acc_bar, 0, 300);
     tc_fence_after_sync();
@@ -101,13 +112,14 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
       if (!row_ok) continue;
       const int c = item.n0 + c0;
       if (Nl == 1) {
-        if (c0 == 0) atomicAdd(dst_row, __uint_as_float(r[0]));
+        if (c0 == 0) dst_row[0] = __uint_as_float(r[0]);
       } else {
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
           if (c + 4 * v < Nl)
-            red_add_v4(dst_row + c + 4 * v, __uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]),
-                       __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
+            *reinterpret_cast<float4*>(dst_row + c + 4 * v) =
+                make_float4(__uint_as_float(r[4 * v]), __uint_as_float(r[4 * v + 1]),
+                            __uint_as_float(r[4 * v + 2]), __uint_as_float(r[4 * v + 3]));
         }
       }
     }

@@ -118,6 +118,19 @@ int dfm_engine_step_from_host(void* engine, const void* host_slab, float* loss_h
  * "uniq_ids","slot_of", and "act"/"dz" with a layer index. */
 int dfm_engine_buffer(void* engine, const char* name, int index, void** ptr, long long* n_elems);
 
+/* Warm CUDA-event timings (ms, means over `iters` real training steps): ms_out[0] forward,
+ * ms_out[1] backward + update, ms_out[2] whole step.  Single-GPU only.  Synchronises. */
+int dfm_engine_profile(void* engine, const int* ids, const float* vals, const float* labels, int iters,
+                       float* ms_out);
+
+/* Multi-GPU (synchronous data parallel, HVD.py:296) without NCCL on the step path: every rank
+ * allocates a symmetric block (comm_alloc, returns a 64-byte CUDA IPC handle), the caller all-gathers
+ * the handles, and comm_attach maps the peers.  From then on train_step fuses the dense gradient
+ * all-reduce into the optimizer kernel and exchanges the sparse embedding gradients with peer
+ * stores over NVLink (csrc/cuda/comm.cu).  All ranks must call train_step the same number of times. */
+int dfm_engine_comm_alloc(void* engine, int world, int rank, void* ipc_handle_out);
+int dfm_engine_comm_attach(void* engine, const void* all_handles);
+
 /* tf.metrics.auc accumulators (HVD.py:271): hist[2][num_thresholds+1] uint64, row 0 positives. */
 int dfm_auc_hist(const float* prob, const float* label, int n, unsigned long long* hist,
                  int num_thresholds, dfm_stream_t stream);

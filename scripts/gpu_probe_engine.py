@@ -85,8 +85,7 @@ def run(B, layers, Ke=32, F=39, V=5000, opt="GD", lr=1.0, l2=0.0, mode="lazy", t
                 ref = torch.where(mask, ref, torch.zeros_like(ref))
             print(f"grad {name:32s}", rel(got, ref))
     print("pending: n_unique", st["n_unique"], "G max", eng.buffer("G").abs().max().item(),
-          "slot_of max", eng.buffer("slot_of", dtype="i4").max().item(),
-          "dense_grad max", eng.buffer("dense_grad").abs().max().item())
+          "slot_of max", eng.buffer("slot_of", dtype="i4").max().item())
     eng.close()
 
 

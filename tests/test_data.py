@@ -1,0 +1,180 @@
+"""Native IO layer: CRC32C, framing, Example codec, sharding, loader, converter, generator.
+Golden facts about the reference's bundled data/val.tfrecords are from SURVEY 2.8."""
+import os
+import struct
+import subprocess
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+from deepfm_b200.data import tfrecord as T
+from deepfm_b200.data.loader import BatchLoader
+from deepfm_b200.data.sharding import hvd_shard, ps_shard, shard_batches_per_epoch
+
+
+def test_crc32c_known_vectors():
+    assert T.crc32c(b"123456789") == 0xE3069283
+    assert T.crc32c(b"") == 0
+    assert T.crc32c(bytes(32)) == 0x8A9136AA
+    c = T.crc32c(b"hello")
+    assert T.masked_crc32c(b"hello") == (((c >> 15) | (c << 17)) + 0xA282EAD8) & 0xFFFFFFFF
+
+
+def test_val_tfrecords_golden_facts(val_tfrecords):
+    if "reference" not in val_tfrecords:
+        pytest.skip("golden numbers are for the reference's bundled file")
+    assert T.count_records(val_tfrecords) == 10000
+    ids, vals, labels = T.read_all(val_tfrecords, 39)
+    assert ids.shape == (10000, 39) and ids.min() == 1 and ids.max() == 117565
+    assert len(np.unique(ids)) == 28116
+    assert abs(labels.mean() - 0.2553) < 1e-4
+    assert (ids[:, :13] == np.arange(1, 14)).all()              # numeric fields: constant ids 1..13
+    assert (vals[:, 13:] == 1.0).all()                          # categorical fields: value 1.0
+    lens = {}
+    order = {"label_first": 0, "values_first": 0}
+    for p in T.iter_records(val_tfrecords):
+        lens[len(p)] = lens.get(len(p), 0) + 1
+        order["label_first" if p.index(b"label") < p.index(b"values") else "values_first"] += 1
+    assert lens == {297: 9038, 298: 952, 299: 10}
+    assert order == {"label_first": 5066, "values_first": 4934}   # key order is not stable
+
+
+@pytest.mark.parametrize("packed", [True, False])
+def test_example_roundtrip_packed_and_unpacked(packed):
+    rng = np.random.default_rng(0)
+    ids = rng.integers(0, 2 ** 40, 39)
+    vals = rng.random(39).astype(np.float32)
+    payload = T.encode_example(1.0, ids, vals, packed=packed)
+    label, i2, v2 = T.parse_example(payload, 39)
+    assert label == 1.0 and (i2 == ids).all() and (v2 == vals).all()
+    _, i32, _ = T.parse_example(T.encode_example(0.0, ids % 100000, vals, packed=packed), 39, ids_dtype=np.int32)
+    assert i32.dtype == np.int32 and (i32 == ids % 100000).all()
+
+
+def test_example_key_order_independent_and_errors():
+    ids, vals = np.arange(5), np.ones(5, np.float32)
+    p = T.encode_example(1.0, ids, vals)
+    # rebuild with the map entries reversed: Example{features{entry*}}
+    body = p[2:] if p[1] < 0x80 else p[3:]
+    entries, pos = [], 0
+    while pos < len(body):
+        assert body[pos] == 0x0A
+        n = body[pos + 1]
+        entries.append(body[pos:pos + 2 + n])
+        pos += 2 + n
+    rev = b"".join(reversed(entries))
+    q = bytes([0x0A, len(rev)]) + rev
+    label, i2, v2 = T.parse_example(q, 5)
+    assert label == 1.0 and (i2 == ids).all()
+    with pytest.raises(T.DataError, match="field_size"):
+        T.parse_example(p, 6)
+    with pytest.raises(T.DataError):
+        T.parse_example(b"\x0a\x05abc", 5)
+
+
+def test_writer_reader_roundtrip_and_corruption(tmp_path):
+    f = str(tmp_path / "a.tfrecords")
+    with T.TFRecordWriter(f) as w:
+        for i in range(100):
+            w.write_example(i % 2, np.arange(39) + i, np.full(39, i, np.float32))
+    assert T.count_records(f) == 100
+    ids, vals, labels = T.read_all(f, 39)
+    assert (ids[7] == np.arange(39) + 7).all() and vals[9, 0] == 9 and labels[3] == 1
+    raw = bytearray(open(f, "rb").read())
+    n = struct.unpack("<Q", raw[:8])[0]
+    assert struct.unpack("<I", raw[8:12])[0] == T.masked_crc32c(bytes(raw[:8]))
+    assert struct.unpack("<I", raw[12 + n:16 + n])[0] == T.masked_crc32c(bytes(raw[12:12 + n]))
+    raw[40] ^= 0xFF
+    open(f, "wb").write(raw)
+    with pytest.raises(T.DataError, match="CRC"):
+        T.count_records(f, verify_crc=True)
+
+
+def test_shard_policies_match_reference_matrix():
+    # (pipe, s3shard, multipath, worker_per_host, hosts, rank, local_rank, world)
+    assert hvd_shard(0, True, False, 4, 1, 2, 2, 4) == (4, 2)       # HVD.py:130-131
+    assert hvd_shard(0, False, False, 4, 1, 2, 2, 4) == (4, 2)      # HVD.py:132-133 (size, rank)
+    assert hvd_shard(0, False, False, 4, 2, 5, 1, 8) == (8, 5)
+    assert hvd_shard(1, True, True, 4, 2, 5, 1, 8) == (1, 0)        # HVD.py:140-141
+    assert hvd_shard(1, False, True, 4, 2, 5, 1, 8) == (2, 1)       # HVD.py:142-144
+    assert hvd_shard(1, False, True, 4, 1, 3, 3, 4) == (1, 0)
+    assert hvd_shard(1, True, False, 4, 2, 5, 1, 8) == (4, 1)       # HVD.py:146-147
+    assert hvd_shard(1, False, False, 4, 2, 5, 1, 8) == (8, 5)      # HVD.py:148-149
+    assert ps_shard(False, ["algo-1", "algo-2"], "algo-2") == (2, 1)   # PS.py:153-156
+    assert ps_shard(True, ["algo-1", "algo-2"], "algo-2") == (1, 0)
+    assert shard_batches_per_epoch(10000, 4, 3, 1024) == 2
+    assert shard_batches_per_epoch(10, 4, 1, 2, drop_remainder=False) == 2
+
+
+def _write(path, n, start=0):
+    with T.TFRecordWriter(path) as w:
+        for i in range(start, start + n):
+            w.write_example(i % 2, np.full(4, i), np.full(4, i, np.float32))
+
+
+def test_loader_shard_batch_repeat_order(tmp_path):
+    a, b = str(tmp_path / "tr_a.tfrecords"), str(tmp_path / "tr_b.tfrecords")
+    _write(a, 50)
+    _write(b, 37, start=50)
+    # shard (3,1) over the concatenated stream, batch 8, drop remainder, 2 epochs
+    got = [hb.feat_ids[:, 0].clone() for hb in BatchLoader([a, b], 4, 8, num_epochs=2, shard_n=3, shard_i=1,
+                                                            ids_dtype=torch.int64, num_workers=3, num_slots=3)]
+    mine = [i for i in range(87) if i % 3 == 1]
+    per_epoch = len(mine) // 8
+    assert len(got) == 2 * per_epoch
+    for e in range(2):
+        for j in range(per_epoch):
+            assert got[e * per_epoch + j].tolist() == mine[j * 8:(j + 1) * 8]
+    # keep the remainder (eval semantics of this framework)
+    tail = [hb.count for hb in BatchLoader([a, b], 4, 8, drop_remainder=False, ids_dtype=torch.int32)]
+    assert sum(tail) == 87 and tail[-1] == 87 % 8
+
+
+def test_loader_reports_bad_records(tmp_path):
+    f = str(tmp_path / "bad.tfrecords")
+    with T.TFRecordWriter(f) as w:
+        w.write_example(1, np.arange(4), np.ones(4, np.float32))
+        w.write_example(1, np.arange(5), np.ones(5, np.float32))     # wrong field count
+    with pytest.raises(T.DataError, match="field_size"):
+        list(BatchLoader([f], 4, 1))
+
+
+def test_pipe_mode_streams_from_fifo(tmp_path):
+    """SageMaker pipe mode (HVD.py:136): records arrive through a FIFO, not a seekable file."""
+    src, fifo = str(tmp_path / "src.tfrecords"), str(tmp_path / "training_0")
+    _write(src, 40)
+    os.mkfifo(fifo)
+    t = threading.Thread(target=lambda: open(fifo, "wb").write(open(src, "rb").read()))
+    t.start()
+    got = [hb.feat_ids[:, 0].tolist() for hb in BatchLoader([fifo], 4, 8, shard_n=2, shard_i=0, streaming=True,
+                                                            ids_dtype=torch.int64)]
+    t.join()
+    assert got == [list(range(0, 16, 2)), list(range(16, 32, 2))]
+
+
+def test_libsvm_converter(tmp_path):
+    txt = tmp_path / "tr.libsvm"
+    txt.write_text("1 1:0.5 2:0.03519 3:1\n0 4:1 5:2.5 6:1\n\n")
+    out = str(tmp_path / "tr.tfrecords")
+    assert T.libsvm_to_tfrecord(str(txt), out, expect_fields=3) == 2
+    ids, vals, labels = T.read_all(out, 3)
+    assert ids.tolist() == [[1, 2, 3], [4, 5, 6]] and labels.tolist() == [1.0, 0.0]
+    assert np.allclose(vals[0], [0.5, 0.03519, 1.0])
+    txt.write_text("1 1:0.5 2:1\n")
+    with pytest.raises(T.DataError, match="expected 3"):
+        T.libsvm_to_tfrecord(str(txt), out, expect_fields=3)
+
+
+def test_synthetic_generator_is_criteo_shaped(tmp_path):
+    f = str(tmp_path / "tr_syn.tfrecords")
+    assert T.generate_synthetic(f, 4096, 39, 117581, n_dense=13, seed=7) == 4096
+    ids, vals, labels = T.read_all(f, 39)
+    assert (ids[:, :13] == np.arange(1, 14)).all() and (vals[:, 13:] == 1.0).all()
+    assert ids.max() < 117581 and ids[:, 13:].min() >= 14
+    assert 0.15 < labels.mean() < 0.40
+    uniq = len(np.unique(ids[:2048]))
+    assert 2000 < uniq < 40000       # skewed: far fewer distinct ids than 2048*39 lookups
+    ids2, _, _ = T.read_all(f, 39)
+    assert (ids2 == ids).all()
