@@ -78,7 +78,7 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
                            size_t part_stride, __nv_bfloat16* __restrict__ Wb, int n,
                            const StepState* __restrict__ st, const OptHyper hyper) {
   const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
-  const unsigned int epoch = unsigned(st->comm_epoch) + 1u;
+  const unsigned int epoch = unsigned(st->comm_epoch);       // bumped by the first kernel of the step
   const int N = cv.world;
   const float inv_n = 1.f / float(N);
   const int n_red = n - 1;                            // element n-1 (fm_bias) shares the gradient of n-2
@@ -159,30 +159,28 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
 __global__ void __launch_bounds__(kCommThreads)
 sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict__ entry_of,
                          int* __restrict__ touched, int* __restrict__ union_ids) {
-  const unsigned int epoch = unsigned(a.st->comm_epoch) + 1u;
+  const unsigned int epoch = unsigned(a.st->comm_epoch);
   const int N = cv.world, Ke = a.Ke, pitch = cv.row_pitch;
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const int warp_g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int n = a.st->n_unique;
 
-  // ---- push: my (id, row) list into inbox[cv.rank] of every rank (own included) ----
+  // ---- push: my (row gradient, first-order gradient, id) records into inbox[cv.rank] of every rank ----
+  // record = g_pitch(Ke) floats: [0,Ke) factor gradients, [Ke] first-order gradient, [Ke+1] id (bit pattern)
   for (int s = warp_g; s < n; s += warps) {
     const int id = a.uniq_ids[s];
-    for (int k = lane; k <= Ke; k += 32) {
-      float v;
-      if (k < Ke) { v = a.G[size_t(s) * Ke + k]; a.G[size_t(s) * Ke + k] = 0.f; }
-      else        { v = a.Gw[s]; a.Gw[s] = 0.f; }
+    float* grow = a.G + size_t(s) * pitch;
+    for (int k = lane; k < pitch; k += 32) {
+      float v = 0.f;
+      if (k <= Ke) { v = grow[k]; grow[k] = 0.f; }
+      else if (k == Ke + 1) v = __int_as_float(id);
       for (int r = 0; r < N; ++r) {
         float* rows = reinterpret_cast<float*>(cv.base[r] + cv.off_in_rows) + (size_t(cv.rank) * cv.cap + s) * pitch;
         rows[k] = v;
       }
     }
-    if (lane == 0) {
-      for (int r = 0; r < N; ++r)
-        reinterpret_cast<int*>(cv.base[r] + cv.off_in_ids)[size_t(cv.rank) * cv.cap + s] = id;
-      a.slot_of[id] = -1;
-    }
+    if (lane == 0) a.slot_of[id] = -1;
   }
   if (threadIdx.x < N)
     reinterpret_cast<int*>(cv.base[threadIdx.x] + cv.off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n;
@@ -190,17 +188,38 @@ sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict_
   cta_barrier_all_ranks(cv, 2, epoch);
 
   // ---- claim: index every received entry by (id, sender) and build the union id list ----
+  // One thread per entry.  The rows pushed by CTA blockIdx.x of rank r are those with
+  // (s % warps) in this CTA's warp range, i.e. s = first_warp + (t % wpc) + (t / wpc) * warps.
   const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_count);
-  const int* in_ids = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_ids);
+  const float* in_rows_c = reinterpret_cast<const float*>(cv.base[cv.rank] + cv.off_in_rows);
+  const int wpc = blockDim.x >> 5;
+  const int first_warp = blockIdx.x * wpc;
+  __shared__ int wsum[kCommThreads / 32];
+  __shared__ int cta_base;
   for (int r = 0; r < N; ++r) {
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
-    // the rows pushed by CTA blockIdx.x of rank r are exactly those this CTA's warps index
-    for (int s = warp_g; s < nr; s += warps) {
-      if (lane == 0) {
-        const int id = ld_volatile_i(in_ids + size_t(r) * cv.cap + s);
+    const int per_cta = (nr > first_warp) ? ((nr - first_warp + warps - 1) / warps) * wpc : 0;   // upper bound
+    for (int t0 = 0; t0 < per_cta; t0 += blockDim.x) {       // uniform trip count for the whole CTA
+      const int t = t0 + threadIdx.x;
+      const int s = first_warp + (t % wpc) + (t / wpc) * warps;
+      int id = 0, won = 0;
+      if (t < per_cta && s < nr) {
+        id = __float_as_int(ld_volatile_f(in_rows_c + (size_t(r) * cv.cap + s) * pitch + Ke + 1));
         entry_of[size_t(id) * N + r] = s + 1;
-        if (atomicCAS(&touched[id], 0, 1) == 0) union_ids[atomicAdd(&a.st->n_union, 1)] = id;
+        won = atomicCAS(&touched[id], 0, 1) == 0;
       }
+      // one n_union bump per CTA round (returning atomics on one address serialise)
+      const unsigned winners = __ballot_sync(0xffffffffu, won);
+      if (lane == 0) wsum[threadIdx.x >> 5] = __popc(winners);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int w = 0; w < wpc; ++w) { const int c = wsum[w]; wsum[w] = tot; tot += c; }
+        cta_base = tot ? atomicAdd(&a.st->n_union, tot) : 0;
+      }
+      __syncthreads();
+      if (won) union_ids[cta_base + wsum[threadIdx.x >> 5] + __popc(winners & ((1u << lane) - 1u))] = id;
+      __syncthreads();
     }
   }
 }
@@ -243,18 +262,6 @@ sparse_merge_apply_kernel(const CommView cv, const SparseArgs a, int* __restrict
       }
     }
     if (lane == 0) touched[id] = 0;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    if (atomicAdd(&a.st->sparse_done, 1) == int(gridDim.x) - 1) {
-      a.st->n_unique = 0;
-      a.st->n_union = 0;
-      a.st->sparse_done = 0;
-      a.st->step += 1;
-      a.st->comm_epoch += 1;
-      __threadfence();
-    }
   }
 }
 

@@ -29,9 +29,17 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kEmbedWarps + warp;
   const int count = st->count;
-  if (blockIdx.x == 0 && threadIdx.x == 0) st->loss_sum = 0.f;   // consumed by mlp_fwd of this step
-  if (b >= count) return;
-
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->loss_sum = 0.f;            // accumulated by the loss kernel of this step
+    if (dedupe) {                  // == training step: open optimizer step (see StepState::step)
+      st->step += 1;
+      st->comm_epoch += 1;
+    }
+  }
+  // the 8 examples of a CTA are one 32-byte sector of fm_part: staged in smem, stored by one thread
+  __shared__ __align__(16) float part_out[kEmbedWarps];
+  const bool active = b < count;
+  if (active) {
   const int* my_ids = ids + size_t(b) * F;
   const float* my_vals = vals + size_t(b) * F;
 
@@ -97,7 +105,19 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
   float tot = yw + 0.5f * yv;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-  if (lane == 0) fm_part[b] = tot + __ldg(fm_bias);
+  if (lane == 0) part_out[warp] = tot + __ldg(fm_bias);
+  }  // active
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int b0 = blockIdx.x * kEmbedWarps;
+    if (b0 + kEmbedWarps <= count) {
+      float4* dst = reinterpret_cast<float4*>(fm_part + b0);
+      dst[0] = make_float4(part_out[0], part_out[1], part_out[2], part_out[3]);
+      dst[1] = make_float4(part_out[4], part_out[5], part_out[6], part_out[7]);
+    } else {
+      for (int i = 0; b0 + i < count; ++i) fm_part[b0 + i] = part_out[i];
+    }
+  }
 }
 
 // Sparse-gradient bookkeeping, off the critical path (runs on the side stream while the forward pass
@@ -120,17 +140,29 @@ dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, in
     const bool leave = ref != i && ref < first + int(blockDim.x) && ref < total && __ldg(ids + ref) == id;
     if (!leave && slot_of[id] == -1 && atomicCAS(&slot_of[id], -1, -2) == -1) won = 1;
   }
+  // one counter bump per CTA: returning atomics on a single address serialise at ~50 ns each
+  __shared__ int warp_base[32];
+  __shared__ int cta_base;
   const unsigned winners = __ballot_sync(0xffffffffu, won);
-  if (winners) {
-    const int leader = __ffs(winners) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(&st->n_unique, __popc(winners));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (won) {
-      const int s = base + __popc(winners & ((1u << lane) - 1u));
-      uniq_ids[s] = id;
-      slot_of[id] = s;
+  const int warp = threadIdx.x >> 5;
+  if (lane == 0) warp_base[warp] = __popc(winners);
+  __syncthreads();
+  if (warp == 0) {
+    int c = warp_base[lane];
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
     }
+    warp_base[lane] = incl - c;
+    if (lane == 31) cta_base = incl ? atomicAdd(&st->n_unique, incl) : 0;
+  }
+  __syncthreads();
+  if (won) {
+    const int s = cta_base + warp_base[warp] + __popc(winners & ((1u << lane) - 1u));
+    uniq_ids[s] = id;
+    slot_of[id] = s;
   }
 }
 

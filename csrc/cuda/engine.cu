@@ -77,8 +77,8 @@ struct Engine {
 static int engine_build(Engine& E) {
   const dfm_engine_config& c = E.cfg;
   DFM_REQUIRE(c.n_layers >= 1 && c.n_layers <= kMaxLayers, "n_layers %d outside [1,%d]", c.n_layers, kMaxLayers);
-  DFM_REQUIRE(c.embedding_size % 16 == 0 && c.embedding_size <= 128,
-              "the fused engine needs embedding_size %% 16 == 0 and <= 128 (got %d)", c.embedding_size);
+  DFM_REQUIRE(c.embedding_size % 16 == 0 && c.embedding_size <= 64,
+              "the fused engine needs embedding_size %% 16 == 0 and <= 64 (got %d)", c.embedding_size);
   DFM_REQUIRE(c.batch_max >= 1 && c.field_size >= 1 && c.feature_size >= 1, "bad batch/field/feature size");
   MlpShape& sh = E.sh;
   sh.L = c.n_layers;
@@ -122,7 +122,7 @@ static int engine_build(Engine& E) {
   if ((rc = E.alloc(&E.prob, rows))) return rc;
   if ((rc = E.alloc(&E.dlogit, rows))) return rc;
   const size_t max_slots = size_t(c.batch_max) * c.field_size;
-  if ((rc = E.alloc(&E.G, max_slots * c.embedding_size))) return rc;
+  if ((rc = E.alloc(&E.G, max_slots * g_pitch(c.embedding_size)))) return rc;
   if ((rc = E.alloc(&E.Gw, max_slots))) return rc;
   if ((rc = E.alloc(&E.uniq_ids, max_slots))) return rc;
   if ((rc = E.alloc(&E.slot_of, size_t(c.feature_size), 0xFF))) return rc;   // all -1
@@ -130,7 +130,7 @@ static int engine_build(Engine& E) {
 
   // ---- kernel attributes ----
   if ((rc = mlp_layer_set_smem())) return rc;
-  if ((rc = embed_bwd_set_smem())) return rc;
+  if ((rc = embed_bwd_set_smem(c.embedding_size))) return rc;
   if ((rc = wgrad_set_smem())) return rc;
 
   // ---- TMA descriptors ----
@@ -179,7 +179,7 @@ static int engine_build(Engine& E) {
   DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_fork0, cudaEventDisableTiming));
 
   StepState init{};
-  init.count = c.batch_max; init.step = 1; init.lr = c.lr; init.train = 1;
+  init.count = c.batch_max; init.step = 0; init.lr = c.lr; init.train = 1;
   DFM_CUDA_CHECK(cudaMemcpy(E.st, &init, sizeof(init), cudaMemcpyHostToDevice));
   if ((rc = launch_cast_weights(E.t.dense, E.Wb, E.n_dense, nullptr))) return rc;
   DFM_CUDA_CHECK(cudaDeviceSynchronize());
@@ -196,11 +196,12 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
     // which is queued behind it on the same side stream
     DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
     DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
+    DFM_CUDA_CHECK(cudaMemsetAsync(&E.st->n_unique, 0, 2 * sizeof(int), E.side));   // n_unique, sparse_done
     if ((rc = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side))) return rc;
   }
   const float* fm_bias = E.t.dense + E.off[sh.L + 1];
   if ((rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], sh.pitch[0], E.s_sum, E.fm_part,
-                                c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, 0, s)))
+                                c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, train, s)))
     return rc;
   for (int l = 0; l < sh.L; ++l) {
     LayerParams lp{};
@@ -267,8 +268,10 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   sa.fm_w = E.t.fm_w; sa.w_s0 = E.t.fm_w_s0; sa.w_s1 = E.t.fm_w_s1;
   sa.G = E.G; sa.Gw = E.Gw; sa.slot_of = E.slot_of; sa.uniq_ids = E.uniq_ids; sa.st = E.st;
   sa.Ke = c.embedding_size; sa.V = c.feature_size; sa.grad_scale = gscale;
-  if (E.comm_ready)
+  if (E.comm_ready) {
+    DFM_CUDA_CHECK(cudaMemsetAsync(&E.st->n_union, 0, sizeof(int), s));
     return launch_sparse_exchange_apply(E.cv, sa, E.entry_of, E.touched, E.union_ids, E.hyper, s);
+  }
   return launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
 }
 
@@ -385,7 +388,7 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   CommView& cv = E->cv;
   cv.world = world; cv.rank = rank;
   cv.cap = E->cfg.batch_max * E->cfg.field_size;
-  cv.row_pitch = round_up(E->cfg.embedding_size + 1, 4);
+  cv.row_pitch = g_pitch(E->cfg.embedding_size);
   cv.dense_ctas = 64;
   cv.sparse_ctas = 148;
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
@@ -534,7 +537,7 @@ extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** pt
   else if (!strcmp(name, "state")) { p = E->st; n = sizeof(StepState) / 4; }
   else if (!strcmp(name, "dense_grad")) { p = E->dP; n = (long long)E->part_stride * E->ksplit; }
   else if (!strcmp(name, "dense_bf16")) { p = E->Wb; n = E->n_dense; }
-  else if (!strcmp(name, "G")) { p = E->G; n = (long long)E->cfg.batch_max * E->cfg.field_size * E->cfg.embedding_size; }
+  else if (!strcmp(name, "G")) { p = E->G; n = (long long)E->cfg.batch_max * E->cfg.field_size * g_pitch(E->cfg.embedding_size); }
   else if (!strcmp(name, "Gw")) { p = E->Gw; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "uniq_ids")) { p = E->uniq_ids; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "slot_of")) { p = E->slot_of; n = E->cfg.feature_size; }

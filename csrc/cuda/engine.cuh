@@ -23,11 +23,11 @@ constexpr int kChunkK = 64;         // K elements per pipeline stage (128 B of b
 // replayed without re-recording kernel arguments.
 struct StepState {
   int count;          // valid rows of the current batch
-  int step;           // optimizer step number, 1-based (TF global_step + 1)
+  int step;           // optimizer steps started so far; inside a training step: 1-based index of this update
   float lr;           // learning rate (already multiplied by world size, HVD.py:171)
   float loss_sum;     // sum of per-example BCE over the batch (this rank)
   int n_unique;       // distinct table rows touched by the current batch
-  int sparse_done;    // CTAs of the sparse-apply kernel that have finished (last one resets)
+  int sparse_done;    // (unused)
   int train;          // 1: dropout active, gradients produced
   int n_union;        // multi-GPU: distinct rows touched by any rank this step
   int comm_epoch;     // multi-GPU: completed collective rounds (flag value of the next round = +1)
@@ -41,6 +41,11 @@ struct OptHyper {
   float ftrl_lr_power, ftrl_l1, ftrl_l2;
   float l2_reg;                  // applied to fm_w / fm_v only (HVD.py:266-267)
 };
+
+// Row pitch (floats) of the compact sparse-gradient buffer G: Ke factor gradients, then the first-order
+// gradient at column Ke, padded to a whole number of 32-byte sectors so no two rows share a sector
+// (4-byte read-modify-writes of one sector from different warps serialise badly on this part).
+__host__ __device__ inline int g_pitch(int Ke) { return Ke + 8; }
 
 struct MlpShape {
   int L;                       // hidden layers
@@ -224,7 +229,7 @@ int launch_dedupe(const int*, int, StepState*, int*, int*, int, cudaStream_t);
 int mlp_layer_set_smem();
 int launch_mlp_layer(bool, const CUtensorMap&, const CUtensorMap&, const LayerParams&, int, cudaStream_t);
 int launch_loss_init(const LossParams&, int, cudaStream_t);
-int embed_bwd_set_smem();
+int embed_bwd_set_smem(int);
 int launch_embed_bwd(const FwdMaps&, const BwdParams&, int, cudaStream_t);
 int wgrad_set_smem();
 int launch_wgrad(const WgradMaps&, const WgradParams&, int, cudaStream_t);

@@ -18,14 +18,24 @@ constexpr int kBwdThreads = 192;
 __device__ __forceinline__ int cdiv(int a, int b) { return (a + b - 1) / b; }
 
 // ---------------------------------------------------------------------------------------------
-constexpr int kEbStages = 4;
+constexpr int kEbStages = 2;                       // K' = N_0 is short (4 chunks for 256 units)
+constexpr uint32_t kEbStage = 16384u + 32768u;     // A [128x64] + B [256x64]
+constexpr int kEbRowBytes = 512 + 16;              // one example's 256-column slab of e (bf16) + pad
+constexpr int kEbMaxFields = 16;                   // fields per slab = 256 / Ke  (Ke >= 16)
+
+__host__ __device__ inline int eb_s_row_bytes(int Ke) { return Ke * 4 + 16; }
 
 __global__ void __launch_bounds__(kBwdThreads, 1)
 embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ BwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t kStage = 16384u + 32768u;   // A [128x64] + B [256x64]
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kEbStages * kStage);
+  uint8_t* e_tile = smem + kEbStages * kEbStage;                       // [128][kEbRowBytes]
+  uint8_t* s_tile = e_tile + kTileM * kEbRowBytes;                     // [128][Ke*4 + 16]
+  const int Ke = p.Ke, F = p.F;
+  const int GP = g_pitch(Ke);
+  const int s_row = eb_s_row_bytes(Ke);
+  int2* meta = reinterpret_cast<int2*>(s_tile + kTileM * s_row);       // [128][16] {slot, x}
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(meta) + kTileM * kEbMaxFields * 8);
   uint64_t* empty_bar = full_bar + kEbStages;
   uint64_t* acc_bar = empty_bar + kEbStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
@@ -60,9 +70,9 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
       for (int kc = 0; kc < num_kc; ++kc) {
         const int s = kc % kEbStages;
         mbar_wait(&empty_bar[s], ((kc / kEbStages) & 1) ^ 1, 100);
-        uint8_t* a_dst = smem + size_t(s) * kStage;
+        uint8_t* a_dst = smem + size_t(s) * kEbStage;
         // B = 256 rows of W_0 as four 64-row boxes (rows past K0 are zero-filled but still counted)
-        mbar_arrive_expect_tx(&full_bar[s], kStage);
+        mbar_arrive_expect_tx(&full_bar[s], kEbStage);
         tma_load_2d(a_dst, &maps.dz[0], &full_bar[s], kc * kChunkK, m0);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -76,7 +86,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         const int s = kc % kEbStages;
         mbar_wait(&full_bar[s], (kc / kEbStages) & 1, 200);
         tc_fence_after_sync();
-        const uint32_t a_addr = smem_u32(smem + size_t(s) * kStage);
+        const uint32_t a_addr = smem_u32(smem + size_t(s) * kEbStage);
         const uint32_t b_addr = a_addr + 16384u;
         const int kk_n = min(4, (N0 - kc * kChunkK + 15) / 16);
         for (int kk = 0; kk < kk_n; ++kk)
@@ -92,37 +102,74 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
     const int b = m0 + row;
     const bool valid = b < count;
     const uint32_t t_row = tmem_base + (uint32_t(q * 32) << 16);
-    const int Ke = p.Ke, F = p.F;
     const float dl = valid ? __ldg(p.dlogit + b) : 0.f;
-    const __nv_bfloat16* e_row = p.act[0] + size_t(valid ? b : 0) * p.sh.pitch[0];
-    const float* s_row = p.s_sum + size_t(valid ? b : 0) * Ke;
-    const int* id_row = p.ids + size_t(valid ? b : 0) * F;
-    const float* x_row = p.vals + size_t(valid ? b : 0) * F;
     const bool all_valid = __all_sync(0xffffffffu, valid);
+    const int f_first = n0 / Ke;
+    const int nf = min(kEbMaxFields, (n_here + Ke - 1) / Ke);
+
+    // ---- while the MMAs run: stage everything the epilogue needs, with all loads in flight at once ----
+    // (1) per-(example, field) metadata: slot of the id, feature value
+    for (int j = 0; j < nf; ++j) {
+      int slot = 0;
+      float x = 0.f;
+      if (valid && f_first + j < F) {
+        x = __ldg(p.vals + size_t(b) * F + f_first + j);
+        slot = p.slot_of[__ldg(p.ids + size_t(b) * F + f_first + j)];
+      }
+      meta[row * kEbMaxFields + j] = make_int2(slot, __float_as_int(x));
+    }
+    // (2) this warp's 32 rows of the e slab: lane j fetches 16-byte granule j of each row (coalesced)
+    {
+      const __nv_bfloat16* e_base = p.act[0] + size_t(m0 + q * 32) * p.sh.pitch[0] + n0;
+      const bool g_ok = n0 + lane * 8 < K0;
+#pragma unroll
+      for (int r0 = 0; r0 < 32; r0 += 8) {
+        uint4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          v[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (g_ok && m0 + q * 32 + r0 + i < count)
+            v[i] = __ldg(reinterpret_cast<const uint4*>(e_base + size_t(r0 + i) * p.sh.pitch[0]) + lane);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          *reinterpret_cast<uint4*>(e_tile + size_t(q * 32 + r0 + i) * kEbRowBytes + lane * 16) = v[i];
+      }
+    }
+    // (3) this warp's 32 rows of sum_f e (contiguous in memory: rows are Ke floats)
+    {
+      const float* s_base = p.s_sum + size_t(m0 + q * 32) * Ke;
+      const int total4 = 32 * Ke / 4;
+      for (int i = lane; i < total4; i += 32) {
+        const int e0 = i * 4, r = e0 / Ke, c = e0 - r * Ke;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m0 + q * 32 + r < count) v = __ldg(reinterpret_cast<const float4*>(s_base) + i);
+        *reinterpret_cast<float4*>(s_tile + size_t(q * 32 + r) * s_row + c * 4) = v;
+      }
+    }
+    __syncwarp();
 
     mbar_wait(acc_bar, 0, 300);
     tc_fence_after_sync();
 
-    int cur_f = -1, slot = 0;
+    const uint8_t* my_e = e_tile + size_t(row) * kEbRowBytes;
+    const float* my_s = reinterpret_cast<const float*>(s_tile + size_t(row) * s_row);
+    int cur_j = -1, slot = 0;
     float x = 0.f;
     bool uniform = false;     // every lane of the warp maps this field to the same slot
     for (int c0 = 0; c0 < n_here; c0 += 16) {
       uint32_t r[16];
       tmem_ld_x16(t_row + c0, r);
       tmem_ld_wait();
-      const int c = n0 + c0;
-      if (c >= K0) break;                       // warp-uniform
-      // a 16-column group lies inside one field when Ke % 16 == 0 (checked by the host)
-      const int f = c / Ke;
-      const int k0 = c - f * Ke;
-      if (f != cur_f) {
-        cur_f = f;
-        slot = 0; x = 0.f;
-        if (valid) {
-          const int id = __ldg(id_row + f);
-          x = __ldg(x_row + f);
-          slot = p.slot_of[id];
-        }
+      if (n0 + c0 >= K0) break;                 // warp-uniform
+      // a 16-column group lies inside one field (Ke % 16 == 0, checked by the host)
+      const int j = c0 / Ke;
+      const int k0 = c0 - j * Ke;
+      if (j != cur_j) {
+        cur_j = j;
+        const int2 mt = meta[row * kEbMaxFields + j];
+        slot = mt.x;
+        x = __int_as_float(mt.y);
         const int s0 = __shfl_sync(0xffffffffu, slot, 0);
         uniform = all_valid && __all_sync(0xffffffffu, slot == s0);
         // first-order weight gradient, once per (example, field)
@@ -130,27 +177,27 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         if (uniform) {
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) gw += __shfl_xor_sync(0xffffffffu, gw, o);
-          if (lane == 0) atomicAdd(p.Gw + slot, gw);
+          if (lane == 0) atomicAdd(p.G + size_t(slot) * GP + Ke, gw);
         } else if (valid) {
-          atomicAdd(p.Gw + slot, gw);
+          atomicAdd(p.G + size_t(slot) * GP + Ke, gw);
         }
       }
       float g[16];
       {
-        uint32_t ev[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (valid) {
-          const uint4 e0 = *reinterpret_cast<const uint4*>(e_row + c);
-          const uint4 e1 = *reinterpret_cast<const uint4*>(e_row + c + 8);
-          ev[0] = e0.x; ev[1] = e0.y; ev[2] = e0.z; ev[3] = e0.w;
-          ev[4] = e1.x; ev[5] = e1.y; ev[6] = e1.z; ev[7] = e1.w;
+        const uint4 e0 = *reinterpret_cast<const uint4*>(my_e + c0 * 2);
+        const uint4 e1 = *reinterpret_cast<const uint4*>(my_e + c0 * 2 + 16);
+        const uint32_t ev[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+        float sv[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 t = *reinterpret_cast<const float4*>(my_s + k0 + 4 * i);
+          sv[4 * i] = t.x; sv[4 * i + 1] = t.y; sv[4 * i + 2] = t.z; sv[4 * i + 3] = t.w;
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&ev[i]);
-          const float s0v = valid ? __ldg(s_row + k0 + 2 * i) : 0.f;
-          const float s1v = valid ? __ldg(s_row + k0 + 2 * i + 1) : 0.f;
-          g[2 * i] = (__uint_as_float(r[2 * i]) + dl * (s0v - __low2float(v))) * x;
-          g[2 * i + 1] = (__uint_as_float(r[2 * i + 1]) + dl * (s1v - __high2float(v))) * x;
+          g[2 * i] = (__uint_as_float(r[2 * i]) + dl * (sv[2 * i] - __low2float(v))) * x;
+          g[2 * i + 1] = (__uint_as_float(r[2 * i + 1]) + dl * (sv[2 * i + 1] - __high2float(v))) * x;
         }
       }
       if (uniform) {
@@ -159,16 +206,16 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         for (int off = 8; off >= 1; off >>= 1) {
           const bool upper = (lane & off) != 0;
 #pragma unroll
-          for (int j = 0; j < off; ++j) {
-            const float send = upper ? g[j] : g[j + off];
-            const float keepv = upper ? g[j + off] : g[j];
-            g[j] = keepv + __shfl_xor_sync(0xffffffffu, send, off);
+          for (int jj = 0; jj < off; ++jj) {
+            const float send = upper ? g[jj] : g[jj + off];
+            const float keepv = upper ? g[jj + off] : g[jj];
+            g[jj] = keepv + __shfl_xor_sync(0xffffffffu, send, off);
           }
         }
         g[0] += __shfl_xor_sync(0xffffffffu, g[0], 16);
-        if (lane < 16) atomicAdd(p.G + size_t(slot) * Ke + k0 + lane, g[0]);
+        if (lane < 16) atomicAdd(p.G + size_t(slot) * GP + k0 + lane, g[0]);
       } else if (valid) {
-        float* dst = p.G + size_t(slot) * Ke + k0;
+        float* dst = p.G + size_t(slot) * GP + k0;
         red_add_v4(dst, g[0], g[1], g[2], g[3]);
         red_add_v4(dst + 4, g[4], g[5], g[6], g[7]);
         red_add_v4(dst + 8, g[8], g[9], g[10], g[11]);
@@ -183,16 +230,19 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
 }
 
 // ------------------------------------- host side -------------------------------------------
-int embed_bwd_smem() { return kEbStages * (16384 + 32768) + 512 + 1024; }
+int embed_bwd_smem(int Ke) {
+  return kEbStages * int(kEbStage) + kTileM * kEbRowBytes + kTileM * eb_s_row_bytes(Ke) + kTileM * kEbMaxFields * 8 + 512 + 1024;
+}
 
-int embed_bwd_set_smem() {
-  DFM_CUDA_CHECK(cudaFuncSetAttribute(embed_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, embed_bwd_smem()));
+int embed_bwd_set_smem(int Ke) {
+  DFM_REQUIRE(embed_bwd_smem(Ke) <= 227 * 1024, "embedding_size %d needs too much shared memory in embed_bwd", Ke);
+  DFM_CUDA_CHECK(cudaFuncSetAttribute(embed_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, embed_bwd_smem(Ke)));
   return DFM_OK;
 }
 
 int launch_embed_bwd(const FwdMaps& maps, const BwdParams& prm, int batch_max, cudaStream_t stream) {
   dim3 grid(ceil_div(batch_max, kTileM), ceil_div(prm.sh.K[0], 256));
-  embed_bwd_kernel<<<grid, kBwdThreads, embed_bwd_smem(), stream>>>(maps, prm);
+  embed_bwd_kernel<<<grid, kBwdThreads, embed_bwd_smem(prm.Ke), stream>>>(maps, prm);
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

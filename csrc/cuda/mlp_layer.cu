@@ -173,48 +173,75 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 // ---------------------------------------------------------------------------------------------
-// One warp per example: y_d = h_L . w_out + b_out ; logit ; prob ; BCE ; dlogit ;
-// dz_{L-1} = (h_L > 0) * dlogit * w_out / keep_{L-1} ; dz_L = [dlogit, 0 ...].
+// Eight examples per warp (4 lanes each), so every 32-byte sector of the per-example outputs (logit,
+// prob, dlogit) is written by exactly one warp in one instruction:
+//   y_d = h_L . w_out + b_out ; logit ; prob ; BCE ; dlogit ;
+//   dz_{L-1} = (h_L > 0) * dlogit * w_out / keep_{L-1} ; dz_L = [dlogit, 0 ...].
 __global__ void __launch_bounds__(256)
 loss_init_kernel(const LossParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * 8 + warp;
+  const int sub = lane >> 2, part = lane & 3;               // example within the warp, quarter of its row
+  const int b = (blockIdx.x * 8 + warp) * 8 + sub;
   const int count = p.st->count;
   __shared__ float block_loss[8];
   float loss = 0.f;
-  if (b < count) {
-    const __nv_bfloat16* h = p.h_last + size_t(b) * p.h_pitch;
-    float yd = 0.f;
-    for (int c = lane; c < p.n_last; c += 32) yd += __bfloat162float(h[c]) * __ldg(p.w_out + c);
+  const bool valid = b < count;
+  const __nv_bfloat16* h = p.h_last + size_t(valid ? b : 0) * p.h_pitch;
+  float yd = 0.f;
+  if (valid)
+    for (int c = part * 8; c < p.n_last; c += 32) {          // 8 consecutive columns (16 bytes) per lane
+      const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + c));
+      const uint32_t w4[4] = {hv.x, hv.y, hv.z, hv.w};
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) yd += __shfl_xor_sync(0xffffffffu, yd, o);
+      for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&w4[i]);
+        if (c + 2 * i < p.n_last) yd += __low2float(v) * __ldg(p.w_out + c + 2 * i);
+        if (c + 2 * i + 1 < p.n_last) yd += __high2float(v) * __ldg(p.w_out + c + 2 * i + 1);
+      }
+    }
+  yd += __shfl_xor_sync(0xffffffffu, yd, 1);
+  yd += __shfl_xor_sync(0xffffffffu, yd, 2);
+  float dl = 0.f;
+  if (valid) {
     const float z = __ldg(p.fm_part + b) + yd + __ldg(p.w_out + p.n_last);
     const float pr = 1.f / (1.f + __expf(-z));
-    float dl = 0.f;
     if (p.labels) {
       const float y = __ldg(p.labels + b);
-      loss = fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
+      if (part == 0) loss = fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
       dl = (pr - y) / float(count);
     }
-    if (lane == 0) {
+    if (part == 0) {
       p.logit[b] = z;
       p.prob[b] = pr;
       if (p.dlogit) p.dlogit[b] = dl;
     }
-    if (p.dz_last) {
-      const bool drop = p.st->train && p.keep_last < 1.f;
-      const float scale = drop ? 1.f / p.keep_last : 1.f;
-      __nv_bfloat16* dz = p.dz_last + size_t(b) * p.n_last;
-      for (int c = lane; c < p.n_last; c += 32)
-        dz[c] = __float2bfloat16(__bfloat162float(h[c]) > 0.f ? dl * __ldg(p.w_out + c) * scale : 0.f);
-      if (lane < 16) p.dz_out[size_t(b) * 16 + lane] = __float2bfloat16(lane == 0 ? dl : 0.f);
-    }
-  } else if (p.dz_last && b < p.rows_pad) {
-    // rows past the batch inside the weight-gradient GEMM's K range must read as zero
-    __nv_bfloat16* dz = p.dz_last + size_t(b) * p.n_last;
-    for (int c = lane; c < p.n_last; c += 32) dz[c] = __float2bfloat16(0.f);
-    if (lane < 16) p.dz_out[size_t(b) * 16 + lane] = __float2bfloat16(0.f);
   }
+  if (p.dz_last && b < p.rows_pad) {
+    // rows past the batch inside the weight-gradient GEMM's K range are written as zeros (dl == 0)
+    const bool drop = p.st->train && p.keep_last < 1.f;
+    const float scale = drop ? 1.f / p.keep_last : 1.f;
+    __nv_bfloat16* dz = p.dz_last + size_t(b) * p.n_last;
+    for (int c = part * 8; c < p.n_last; c += 32) {
+      uint4 hv = make_uint4(0u, 0u, 0u, 0u);
+      if (valid) hv = __ldg(reinterpret_cast<const uint4*>(h + c));
+      const uint32_t w4[4] = {hv.x, hv.y, hv.z, hv.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&w4[i]);
+        const float d0 = (c + 2 * i < p.n_last && __low2float(v) > 0.f) ? dl * __ldg(p.w_out + c + 2 * i) * scale : 0.f;
+        const float d1 = (c + 2 * i + 1 < p.n_last && __high2float(v) > 0.f) ? dl * __ldg(p.w_out + c + 2 * i + 1) * scale : 0.f;
+        o[i] = pack_bf16x2(d0, d1);
+      }
+      *reinterpret_cast<uint4*>(dz + c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+    // dz_L row: 16 bf16 = 32 bytes = two 16-byte halves, written by parts 0 and 1
+    if (part < 2)
+      *reinterpret_cast<uint4*>(p.dz_out + size_t(b) * 16 + part * 8) =
+          make_uint4(part == 0 ? pack_bf16x2(dl, 0.f) : 0u, 0u, 0u, 0u);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
   if (lane == 0) block_loss[warp] = loss;
   __syncthreads();
   if (threadIdx.x == 0 && p.labels) {
@@ -244,7 +271,7 @@ int launch_mlp_layer(bool backward, const CUtensorMap& tmA, const CUtensorMap& t
 }
 
 int launch_loss_init(const LossParams& p, int rows_pad, cudaStream_t stream) {
-  loss_init_kernel<<<ceil_div(rows_pad, 8), 256, 0, stream>>>(p);
+  loss_init_kernel<<<ceil_div(rows_pad, 64), 256, 0, stream>>>(p);
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

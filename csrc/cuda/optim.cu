@@ -13,6 +13,8 @@
 
 namespace dfm {
 
+// `step` is the number of COMPLETED optimizer steps; the first kernel of a training step bumps it, so
+// every later kernel of that step reads the 1-based index of the update in flight.
 __global__ void set_state_kernel(StepState* st, int count, float lr, int train, int step) {
   st->count = count;
   st->lr = lr;
@@ -56,34 +58,25 @@ sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
   const int n = a.st->n_unique;
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int GP = g_pitch(a.Ke);
   for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < n; s += warps) {
     const int id = a.uniq_ids[s];
+    float* grow = a.G + size_t(s) * GP;
     for (int k = lane; k < a.Ke; k += 32) {
-      const size_t gi = size_t(s) * a.Ke + k, pi = size_t(id) * a.Ke + k;
+      const size_t pi = size_t(id) * a.Ke + k;
       float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
-      const float g = a.G[gi] * a.grad_scale + hyper.l2_reg * p;
-      a.G[gi] = 0.f;
+      const float g = grow[k] * a.grad_scale + hyper.l2_reg * p;
+      grow[k] = 0.f;
       opt_apply(c, g, p, m, v);
       a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
     }
     if (lane == 0) {
       float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
-      const float g = a.Gw[s] * a.grad_scale + hyper.l2_reg * p;
-      a.Gw[s] = 0.f;
+      const float g = grow[a.Ke] * a.grad_scale + hyper.l2_reg * p;    // first-order gradient rides in the row
+      grow[a.Ke] = 0.f;
       opt_apply(c, g, p, m, v);
       a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
       a.slot_of[id] = -1;
-    }
-  }
-  // the last CTA to finish closes the step
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    if (atomicAdd(&a.st->sparse_done, 1) == int(gridDim.x) - 1) {
-      a.st->n_unique = 0;
-      a.st->sparse_done = 0;
-      a.st->step += 1;
-      __threadfence();
     }
   }
 }
@@ -101,8 +94,8 @@ table_dense_kernel(const SparseArgs a, const OptHyper hyper) {
       float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
       float g = hyper.l2_reg * p;
       if (s >= 0) {
-        g += a.G[size_t(s) * a.Ke + k] * a.grad_scale;
-        a.G[size_t(s) * a.Ke + k] = 0.f;
+        g += a.G[size_t(s) * g_pitch(a.Ke) + k] * a.grad_scale;
+        a.G[size_t(s) * g_pitch(a.Ke) + k] = 0.f;
       }
       opt_apply(c, g, p, m, v);
       a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
@@ -112,22 +105,12 @@ table_dense_kernel(const SparseArgs a, const OptHyper hyper) {
       float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
       float g = hyper.l2_reg * p;
       if (s >= 0) {
-        g += a.Gw[s] * a.grad_scale;
-        a.Gw[s] = 0.f;
+        g += a.G[size_t(s) * g_pitch(a.Ke) + a.Ke] * a.grad_scale;
+        a.G[size_t(s) * g_pitch(a.Ke) + a.Ke] = 0.f;
         a.slot_of[id] = -1;
       }
       opt_apply(c, g, p, m, v);
       a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
-    }
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    if (atomicAdd(&a.st->sparse_done, 1) == int(gridDim.x) - 1) {
-      a.st->n_unique = 0;
-      a.st->sparse_done = 0;
-      a.st->step += 1;
-      __threadfence();
     }
   }
 }
@@ -192,7 +175,7 @@ int launch_sparse_apply(const SparseArgs& a, const OptHyper& h, int max_rows, bo
     const int grid = int(std::min<long long>(148 * 8, (warps_needed + 7) / 8));
     table_dense_kernel<<<grid, 256, 0, stream>>>(a, h);
   } else {
-    const int grid = std::max(1, std::min(148 * 8, ceil_div(max_rows, 8)));
+    const int grid = std::max(1, std::min(148 * 4, ceil_div(max_rows, 8)));
     sparse_apply_kernel<<<grid, 256, 0, stream>>>(a, h);
   }
   DFM_LAUNCH_CHECK();

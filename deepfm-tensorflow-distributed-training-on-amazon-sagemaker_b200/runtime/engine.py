@@ -60,8 +60,8 @@ def fused_engine_supported(cfg: DeepFMConfig) -> Optional[str]:
         return "batch_norm needs batch-wide statistics between layers; it runs on the layered path"
     if cfg.loss_type != "log_loss":
         return "the fused loss epilogue implements log_loss only"
-    if cfg.embedding_size % 16 or cfg.embedding_size > 128:
-        return "embedding_size must be a multiple of 16 and <= 128"
+    if cfg.embedding_size % 16 or cfg.embedding_size > 64:
+        return "embedding_size must be a multiple of 16 and <= 64"
     if not 1 <= len(cfg.deep_layers) <= MAX_LAYERS:
         return f"1..{MAX_LAYERS} deep layers"
     if max(cfg.deep_layers) > 512:

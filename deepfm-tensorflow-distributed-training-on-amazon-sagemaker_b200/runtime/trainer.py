@@ -123,7 +123,7 @@ class Trainer:
         self.global_step = int(step.item())
         if self.backend == "fused":
             self.engine.sync_weights()
-            self.engine.set_state(self.opts.batch_size, train=True, step=self.global_step + 1)
+            self.engine.set_state(self.opts.batch_size, train=True, step=self.global_step)
 
     # ------------------------------------------------------------------ state
     def variables(self) -> "OrderedDict[str, torch.Tensor]":
@@ -166,7 +166,7 @@ class Trainer:
         self.global_step = int(step)
         if self.backend == "fused":
             self.engine.sync_weights()
-            self.engine.set_state(self.opts.batch_size, train=True, step=self.global_step + 1)
+            self.engine.set_state(self.opts.batch_size, train=True, step=self.global_step)
         else:
             self.optimizer.step = self.global_step
         return missing
@@ -339,7 +339,7 @@ class Trainer:
         reg = 0.0
         v = self.variables()
         l2 = self.cfg.l2_reg
-        reg = float(l2 * 0.5 * (v["fm_w"].float().pow(2).sum() + v["fm_v"].float().pow(2).sum()))
+        reg = float(l2 * 0.5 * (v["fm_w"].detach().float().pow(2).sum() + v["fm_v"].detach().float().pow(2).sum()))
         out = {"loss": loss_sum / max(n, 1) + reg, "data_loss": loss_sum / max(n, 1), "examples": n,
                "global_step": self.global_step}
         if self.backend == "fused" and self.uses_graph:

@@ -58,7 +58,7 @@ def run(B, layers, Ke=32, F=39, V=5000, opt="GD", lr=1.0, l2=0.0, mode="lazy", t
 
     # ---------------- one GD step == gradients ----------------
     before = {k: v.clone() for k, v in eng.variables().items()}
-    eng.set_state(B, train=True, step=1)
+    eng.set_state(B, train=True, step=0)
     eng.train_step(ids32, vals, labels, set_state=False)
     torch.cuda.synchronize()
     st = eng.read_state()

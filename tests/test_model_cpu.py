@@ -1,0 +1,159 @@
+"""Oracle model math, TF-formula optimizers, AUC, export -- all on CPU."""
+import numpy as np
+import pytest
+import torch
+
+from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+from deepfm_b200.utils.metrics import StreamingAUC, exact_auc, tf_auc_numpy
+from deepfm_b200.utils.optimizers import TFOptimizer, canonical_optimizer
+
+
+def test_forward_matches_hand_written_numpy():
+    cfg = DeepFMConfig(field_size=5, feature_size=50, embedding_size=4, deep_layers=[8, 4], dropout_keep=[1, 1])
+    m = DeepFM(cfg, seed=3)
+    with torch.no_grad():
+        for p in m.parameters():
+            p.copy_(torch.randn_like(p) * 0.3)
+    ids = torch.tensor([[1, 2, 3, 4, 4], [9, 8, 7, 6, 5]])
+    vals = torch.rand(2, 5)
+    got = m(ids, vals).detach().numpy()
+    W = {k: v.detach().numpy() for k, v in m.tf_variables().items()}
+    x, i = vals.numpy(), ids.numpy()
+    y_w = (W["fm_w"][i] * x).sum(1)
+    e = W["fm_v"][i] * x[..., None]
+    y_v = 0.5 * ((e.sum(1) ** 2) - (e ** 2).sum(1)).sum(1)
+    h = e.reshape(2, -1)
+    for l in range(2):
+        h = np.maximum(h @ W[f"Deep-part/mlp{l}/weights"] + W[f"Deep-part/mlp{l}/biases"], 0)
+    y = W["fm_bias"] + y_w + y_v + (h @ W["Deep-part/deep_out/weights"]).reshape(-1) + W["Deep-part/deep_out/biases"]
+    np.testing.assert_allclose(got, y, rtol=1e-5, atol=1e-5)
+    labels = torch.tensor([1.0, 0.0])
+    loss = m.loss(m(ids, vals), labels).item()
+    bce = np.mean(np.maximum(y, 0) - y * labels.numpy() + np.log1p(np.exp(-np.abs(y))))
+    reg = cfg.l2_reg * 0.5 * ((W["fm_w"] ** 2).sum() + (W["fm_v"] ** 2).sum())
+    assert abs(loss - (bce + reg)) < 1e-5
+
+
+def test_variable_names_and_shapes_follow_the_reference_graph():
+    cfg = DeepFMConfig(39, 117581, 32, [256, 128, 64], [0.5] * 3, batch_norm=True)
+    m = DeepFM(cfg, seed=0)
+    v = m.tf_variables()
+    assert tuple(v["fm_bias"].shape) == (1,) and tuple(v["fm_w"].shape) == (117581,)
+    assert tuple(v["fm_v"].shape) == (117581, 32)
+    assert tuple(v["Deep-part/mlp0/weights"].shape) == (1248, 256)
+    assert tuple(v["Deep-part/mlp2/biases"].shape) == (64,)
+    assert tuple(v["Deep-part/deep_out/weights"].shape) == (64, 1)
+    for leaf in ("beta", "gamma", "moving_mean", "moving_variance"):
+        assert tuple(v[f"Deep-part/bn_1/{leaf}"].shape) == (128,)
+    assert DeepFM(DeepFMConfig(39, 117581), seed=0).num_parameters() == 4241135
+    # initialisers: glorot normal on the FM tables, zeros on biases
+    assert abs(m.fm_v.std().item() - (2 / (117581 + 32)) ** 0.5) < 3e-4 and m.fm_bias.item() == 0
+
+
+def test_dropout_is_keep_probability_and_bn_follows_relu():
+    cfg = DeepFMConfig(4, 20, 4, [64], [0.25], batch_norm=True, batch_norm_decay=0.9)
+    m = DeepFM(cfg, seed=0)
+    ids, vals = torch.randint(0, 20, (512, 4)), torch.rand(512, 4)
+    before = m.bn_mean_0.clone()
+    m(ids, vals, training=False)
+    assert torch.equal(m.bn_mean_0, before)                       # eval never touches the moving stats (Q5)
+    m(ids, vals, training=True)
+    assert not torch.equal(m.bn_mean_0, before)
+    y_w, y_v, e = m.fm_terms(ids, vals)
+    h = torch.relu(e.reshape(512, -1) @ m.mlp_w[0] + m.mlp_b[0])
+    assert torch.allclose(m.bn_mean_0, 0.1 * h.mean(0), atol=1e-6)    # decay 0.9 from zero
+    torch.manual_seed(0)
+    cfg2 = DeepFMConfig(4, 20, 4, [4096], [0.25])
+    m2 = DeepFM(cfg2, seed=0)
+    with torch.no_grad():
+        m2.mlp_b[0].fill_(1.0)
+    e = m2.fm_terms(ids[:8], vals[:8])[2].reshape(8, -1)
+    h = torch.relu(e @ m2.mlp_w[0] + m2.mlp_b[0])
+    hd = torch.nn.functional.dropout(h, p=0.75, training=True)
+    assert 0.22 < (hd != 0).float().mean().item() / (h != 0).float().mean().item() < 0.28
+
+
+def _np_step(kind, p, g, s0, s1, lr, t):
+    if kind == "adam":
+        b1, b2, eps = 0.9, 0.999, 1e-8
+        s0 = b1 * s0 + (1 - b1) * g
+        s1 = b2 * s1 + (1 - b2) * g * g
+        lr_t = lr * np.sqrt(1 - b2 ** t) / (1 - b1 ** t)
+        p = p - lr_t * s0 / (np.sqrt(s1) + eps)
+    elif kind == "adagrad":
+        s0 = s0 + g * g
+        p = p - lr * g / np.sqrt(s0)
+    elif kind == "momentum":
+        s0 = 0.95 * s0 + g
+        p = p - lr * s0
+    elif kind == "ftrl":
+        new = s0 + g * g
+        sigma = (np.sqrt(new) - np.sqrt(s0)) / lr
+        s1 = s1 + g - sigma * p
+        p = -s1 / (np.sqrt(new) / lr)
+        s0 = new
+    else:
+        p = p - lr * g
+    return p, s0, s1
+
+
+@pytest.mark.parametrize("kind", ["adam", "adagrad", "momentum", "ftrl", "gd"])
+def test_optimizers_match_tf_update_formulas(kind):
+    rng = np.random.default_rng(1)
+    p0 = rng.standard_normal(64).astype(np.float64)
+    opt = TFOptimizer(kind, lr=0.05)
+    p = torch.tensor(p0.copy())
+    i0, i1 = opt.slot_init_values()
+    s0, s1 = np.full(64, i0), np.full(64, i1)
+    pn = p0.copy()
+    for t in range(1, 6):
+        g = rng.standard_normal(64)
+        opt.apply_dense("w", p, torch.tensor(g))
+        opt.finish_step()
+        pn, s0, s1 = _np_step(kind, pn, g, s0, s1, 0.05, t)
+    np.testing.assert_allclose(p.numpy(), pn, rtol=1e-9, atol=1e-12)
+    names = [n for n in opt.slot_names("w") if n]
+    assert names == {"adam": ["w/Adam", "w/Adam_1"], "adagrad": ["w/Adagrad"], "momentum": ["w/Momentum"],
+                     "ftrl": ["w/Ftrl", "w/Ftrl_1"], "gd": []}[kind]
+
+
+def test_lazy_rows_only_touch_their_rows():
+    opt = TFOptimizer("Adam", 0.1)
+    p = torch.ones(10, 4)
+    rows = torch.tensor([2, 7])
+    opt.apply_rows("fm_v", p, rows, torch.ones(2, 4))
+    assert (p[[0, 1, 3, 4, 5, 6, 8, 9]] == 1).all() and (p[rows] < 1).all()
+    assert (opt.slots["fm_v/Adam"][[0, 1]] == 0).all() and (opt.slots["fm_v/Adam"][rows] != 0).all()
+    assert canonical_optimizer("GD") == "gd" and canonical_optimizer("ftrl") == "ftrl"
+
+
+def test_auc_modes():
+    from sklearn.metrics import roc_auc_score
+    rng = np.random.default_rng(0)
+    p = rng.random(20000).astype(np.float32)
+    y = (rng.random(20000) < p).astype(np.float32)
+    assert abs(exact_auc(y, p) - roc_auc_score(y, p)) < 1e-12
+    assert abs(tf_auc_numpy(y, p) - roc_auc_score(y, p)) < 2e-3       # 200-threshold trapezoid approximation
+    s = StreamingAUC()
+    for i in range(0, 20000, 1024):
+        s.update(y[i:i + 1024], p[i:i + 1024])
+    assert abs(s.result() - tf_auc_numpy(y, p)) < 1e-12 and abs(s.result_exact() - exact_auc(y, p)) < 1e-12
+    # ties and degenerate inputs
+    assert exact_auc(np.array([0, 1, 0, 1.0]), np.array([0.5, 0.5, 0.5, 0.5])) == 0.5
+    assert np.isnan(exact_auc(np.ones(4), np.random.rand(4)))
+
+
+def test_export_and_serving_signature(tmp_path):
+    from deepfm_b200.utils.export import export_servable, load_servable
+    cfg = DeepFMConfig(39, 500, 8, [16, 8], [0.5, 0.5])
+    m = DeepFM(cfg, seed=5)
+    out = export_servable(m, str(tmp_path / "servable"), timestamp=1600000000)
+    assert out.endswith("1600000000")
+    assert export_servable(m, str(tmp_path / "servable"), timestamp=1600000000).endswith("1600000001")
+    serve = load_servable(str(tmp_path / "servable"))
+    ids = np.random.randint(0, 500, (7, 39)).astype(np.int64)
+    vals = np.random.rand(7, 39).astype(np.float32)
+    got = serve(ids, vals)
+    assert set(got) == {"prob"} and got["prob"].shape == (7,) and got["prob"].dtype == np.float32
+    ref = torch.sigmoid(m(torch.from_numpy(ids), torch.from_numpy(vals))).detach().numpy()
+    np.testing.assert_allclose(got["prob"], ref, rtol=1e-6)
