@@ -1,0 +1,16 @@
+// Shared between unique.cu (caller-provided workspace) and its static-workspace variant.
+#pragma once
+
+#include "engine.cuh"
+
+namespace dfm {
+
+constexpr int kUniqueHeaderInts = 64;   // 256 bytes: the StepState the claim kernel counts in, padded
+
+// Header cleared, id -> slot map set to -1.  Stream-ordered, no allocation.
+int unique_workspace_init(void* workspace, long long V, cudaStream_t stream);
+// Claim + per-position lookup + map restore.  `workspace` must have been initialised once.
+int unique_slots_run(const int* ids, int n, void* workspace, int* uniq_out, int* pos_slot_out, int* count_out,
+                     cudaStream_t stream);
+
+}  // namespace dfm

@@ -131,6 +131,19 @@ int dfm_engine_profile(void* engine, const int* ids, const float* vals, const fl
 int dfm_engine_comm_alloc(void* engine, int world, int rank, void* ipc_handle_out);
 int dfm_engine_comm_attach(void* engine, const void* all_handles);
 
+/* ------------------------------------------------------------------------
+ * De-duplication of a batch's feature ids (the step that turns B*F row gradients into n_unique
+ * rows before they are communicated or applied; TF's IndexedSlices path has no such step,
+ * HVD.py:197,201 + SURVEY K13).  ids int32 [n] in [0, V).  Outputs: uniq_out [<= n] distinct ids,
+ * pos_slot_out [n] with uniq_out[pos_slot_out[i]] == ids[i], count_out [1].
+ * `workspace` is caller-owned scratch of dfm_unique_slots_workspace_bytes(V) bytes, initialised once
+ * with dfm_unique_slots_init; every call leaves it ready for the next one.
+ * ---------------------------------------------------------------------- */
+long long dfm_unique_slots_workspace_bytes(long long V);
+int dfm_unique_slots_init(void* workspace, long long V, dfm_stream_t stream);
+int dfm_unique_slots(const int* ids, int n, long long V, void* workspace, int* uniq_out, int* pos_slot_out,
+                     int* count_out, dfm_stream_t stream);
+
 /* tf.metrics.auc accumulators (HVD.py:271): hist[2][num_thresholds+1] uint64, row 0 positives. */
 int dfm_auc_hist(const float* prob, const float* label, int n, unsigned long long* hist,
                  int num_thresholds, dfm_stream_t stream);
