@@ -144,6 +144,20 @@ int dfm_unique_slots_init(void* workspace, long long V, dfm_stream_t stream);
 int dfm_unique_slots(const int* ids, int n, long long V, void* workspace, int* uniq_out, int* pos_slot_out,
                      int* count_out, dfm_stream_t stream);
 
+/* dfm_unique_slots without a workspace argument and without any device allocation, for callers that
+ * may not allocate GPU memory: plug-ins living in a process whose GPU memory is already owned by
+ * another framework's allocator, or loops that cannot take the device-wide synchronisation of
+ * cudaMalloc/cudaFree.  (No counterpart in the reference: TensorFlow allocates for its ops.)
+ * The scratch is a 4 MiB array compiled into the library and resident on every GPU that loads it,
+ * which caps the id space at DFM_UNIQUE_STATIC_MAX_V; a larger V is rejected with an error.
+ * The first call on each device looks the array up and fills it with -1 on `stream`: make that call
+ * before any stream capture.  All calls on a device share the array: calls issued back to back on
+ * one stream are fine, calls that overlap on the GPU race.  Same inputs/outputs as dfm_unique_slots. */
+#define DFM_UNIQUE_STATIC_MAX_V (1 << 20)
+long long dfm_unique_slots_static_max_v(void);
+int dfm_unique_slots_static(const int* ids, int n, long long V, int* uniq_out, int* pos_slot_out,
+                            int* count_out, dfm_stream_t stream);
+
 /* tf.metrics.auc accumulators (HVD.py:271): hist[2][num_thresholds+1] uint64, row 0 positives. */
 int dfm_auc_hist(const float* prob, const float* label, int n, unsigned long long* hist,
                  int num_thresholds, dfm_stream_t stream);
