@@ -21,7 +21,9 @@
 
 namespace dfm {
 
-constexpr int kCommThreads = 256;
+constexpr int kCommThreads = 512;      // dense all-reduce kernel
+constexpr int kOneShotMaxRanks = 4;    // up to here every rank reduces the whole dense gradient itself
+constexpr int kSparseThreads = 1024;   // sparse exchange kernels: one warp per row, rows are latency-bound
 constexpr long long kCommWatchdog = 10000000000LL;   // ~5 s
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
@@ -48,25 +50,47 @@ __device__ __forceinline__ int ld_volatile_i(const int* p) {
   return v;
 }
 
+__device__ __forceinline__ void stamp(const CommView& cv, int slot) {
+  if (blockIdx.x == 0 && threadIdx.x == 0 && cv.dbg) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    cv.dbg[slot] = t;
+  }
+}
+
 // Barrier among the CTAs with index blockIdx.x of all ranks.  `slot` selects one of the flag arrays.
 // Everything the calling CTA wrote before (to any GPU) is visible to its peers' matching CTA after.
+__device__ __forceinline__ unsigned int ld_relaxed_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 __device__ __forceinline__ void cta_barrier_all_ranks(const CommView& cv, int slot, unsigned int epoch) {
-  __threadfence_system();
+  // bar.sync orders every thread's earlier writes before the signalling threads, and their release
+  // store at system scope is cumulative over those writes: no separate membar.sys is needed (measured:
+  // a system fence costs ~4 us here, and st.release.sys contains one).
   __syncthreads();
+  if (slot == 0) stamp(cv, 16);
   const int t = threadIdx.x;
   if (t < cv.world) {
     unsigned int* peer_flags = reinterpret_cast<unsigned int*>(cv.base[t] + cv.off_flags);
+    if (slot == 0) stamp(cv, 17);
     st_release_sys(peer_flags + (size_t(slot) * cv.world + cv.rank) * kCommMaxCtas + blockIdx.x, epoch);
     const unsigned int* mine = reinterpret_cast<const unsigned int*>(cv.base[cv.rank] + cv.off_flags) +
                                (size_t(slot) * cv.world + t) * kCommMaxCtas + blockIdx.x;
+    if (slot == 0) stamp(cv, 18);
     const long long t0 = clock64();
-    while (ld_acquire_sys(mine) < epoch) {
+    while (ld_relaxed_sys(mine) < epoch) {
       if (clock64() - t0 > kCommWatchdog) {
         printf("[dfm comm watchdog] rank %d cta %d slot %d waiting for rank %d epoch %u\n", cv.rank, blockIdx.x,
                slot, t, epoch);
         __trap();
       }
     }
+    if (slot == 0) stamp(cv, 19);
+    (void)ld_acquire_sys(mine);        // one acquire once the flag is up: peers' writes are visible from here
+    if (slot == 0) stamp(cv, 20);
   }
   __syncthreads();
 }
@@ -89,6 +113,7 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
   float* my_dP = reinterpret_cast<float*>(cv.base[cv.rank] + cv.off_dP);
   float* my_avg = reinterpret_cast<float*>(cv.base[cv.rank] + cv.off_avg);
 
+  stamp(cv, 0);
   // local: add the split-K slices of the weight-gradient GEMM into the symmetric gradient buffer.
   // CTA b sums exactly the groups that the peers' CTA b will read, so the per-CTA barrier below is enough.
   for (int r = 0; r < N; ++r) {
@@ -105,7 +130,43 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
   }
 
   // A: every rank's local gradients are complete -> safe to read them remotely
+  stamp(cv, 1);
   cta_barrier_all_ranks(cv, 0, epoch);
+  stamp(cv, 2);
+
+  if (N <= kOneShotMaxRanks) {
+    // one-shot: every rank reads every peer's gradient itself and applies the update -- one barrier
+    // instead of two; the extra NVLink reads (N-1 x 1.4 MB) are cheaper than a second system fence.
+    for (int r = 0; r < N; ++r) {
+      const int g0 = r * shard4 + blockIdx.x * sub4;
+      const int g1 = min(min(g0 + sub4, (r + 1) * shard4), n4);
+      for (int g = g0 + threadIdx.x; g < g1; g += blockDim.x) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+        for (int q = 0; q < N; ++q) {               // rank order: identical sum on every replica
+          const float4 v = ld_volatile_f4(reinterpret_cast<const float*>(cv.base[q] + cv.off_dP) + 4 * size_t(g));
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        const float gr[4] = {acc.x * inv_n, acc.y * inv_n, acc.z * inv_n, acc.w * inv_n};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int i = 4 * g + j;
+          if (i >= n_red) break;
+          float p = P[i], a = s0[i], b = s1[i];
+          opt_apply(c, gr[j], p, a, b);
+          P[i] = p; s0[i] = a; s1[i] = b;
+          Wb[i] = __float2bfloat16(p);
+          if (i == n - 2) {
+            float p2 = P[n - 1], a2 = s0[n - 1], b2 = s1[n - 1];
+            opt_apply(c, gr[j], p2, a2, b2);
+            P[n - 1] = p2; s0[n - 1] = a2; s1[n - 1] = b2;
+          }
+        }
+      }
+    }
+    stamp(cv, 5);
+    return;
+  }
 
   // reduce-scatter my shard, fused with the 1/N scale; all-gather by storing to every peer
   {
@@ -125,7 +186,9 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
 
   // B: the averaged slices written by CTA blockIdx.x of every rank have landed here, and every peer
   //    has finished reading the matching slices of my gradient buffer
+  stamp(cv, 3);
   cta_barrier_all_ranks(cv, 1, epoch);
+  stamp(cv, 4);
 
   for (int r = 0; r < N; ++r) {
     const int g0 = r * shard4 + blockIdx.x * sub4;
@@ -149,6 +212,7 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
       }
     }
   }
+  stamp(cv, 5);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -156,7 +220,7 @@ dense_allreduce_opt_kernel(const CommView cv, float* __restrict__ P, float* __re
 //   count   int[world]                    at off_in_count
 //   ids     int  [world][cap]             at off_in_ids
 //   rows    float[world][cap][row_pitch]  at off_in_rows     row = Ke gradient values, then gw
-__global__ void __launch_bounds__(kCommThreads)
+__global__ void __launch_bounds__(kSparseThreads)
 sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict__ entry_of,
                          int* __restrict__ touched, int* __restrict__ union_ids) {
   const unsigned int epoch = unsigned(a.st->comm_epoch);
@@ -166,6 +230,7 @@ sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict_
   const int warp_g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int n = a.st->n_unique;
 
+  stamp(cv, 8);
   // ---- push: my (row gradient, first-order gradient, id) records into inbox[cv.rank] of every rank ----
   // record = g_pitch(Ke) floats: [0,Ke) factor gradients, [Ke] first-order gradient, [Ke+1] id (bit pattern)
   for (int s = warp_g; s < n; s += warps) {
@@ -185,7 +250,9 @@ sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict_
   if (threadIdx.x < N)
     reinterpret_cast<int*>(cv.base[threadIdx.x] + cv.off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n;
 
+  stamp(cv, 9);
   cta_barrier_all_ranks(cv, 2, epoch);
+  stamp(cv, 10);
 
   // ---- claim: index every received entry by (id, sender) and build the union id list ----
   // One thread per entry.  The rows pushed by CTA blockIdx.x of rank r are those with
@@ -194,7 +261,7 @@ sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict_
   const float* in_rows_c = reinterpret_cast<const float*>(cv.base[cv.rank] + cv.off_in_rows);
   const int wpc = blockDim.x >> 5;
   const int first_warp = blockIdx.x * wpc;
-  __shared__ int wsum[kCommThreads / 32];
+  __shared__ int wsum[kSparseThreads / 32];
   __shared__ int cta_base;
   for (int r = 0; r < N; ++r) {
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
@@ -222,9 +289,10 @@ sparse_push_claim_kernel(const CommView cv, const SparseArgs a, int* __restrict_
       __syncthreads();
     }
   }
+  stamp(cv, 11);
 }
 
-__global__ void __launch_bounds__(kCommThreads)
+__global__ void __launch_bounds__(kSparseThreads)
 sparse_merge_apply_kernel(const CommView cv, const SparseArgs a, int* __restrict__ entry_of,
                           int* __restrict__ touched, const int* __restrict__ union_ids, const OptHyper hyper) {
   const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
@@ -233,36 +301,77 @@ sparse_merge_apply_kernel(const CommView cv, const SparseArgs a, int* __restrict
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const int n = a.st->n_union;
+  // the inbox was written by peers before the push barrier of the previous kernel; this is a new launch
+  // (L1 starts empty), so plain L2 loads see it
   const float* in_rows = reinterpret_cast<const float*>(cv.base[cv.rank] + cv.off_in_rows);
+  stamp(cv, 12);
 
-  for (int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; u < n; u += warps) {
-    const int id = union_ids[u];
-    int ent = 0;
-    if (lane < N) {
-      ent = entry_of[size_t(id) * N + lane];
-      entry_of[size_t(id) * N + lane] = 0;
+  // The work per row is a chain of dependent loads (id -> entries -> inbox rows -> table row), so each
+  // warp keeps kRows rows in flight: every stage is issued for all of them before any result is used.
+  constexpr int kRows = 2;
+  constexpr int kKPL = 2;                            // embedding components per lane (Ke <= 64)
+  for (int u0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kRows; u0 < n; u0 += warps * kRows) {
+    int id[kRows], ent[kRows];
+    bool live[kRows];
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      live[j] = u0 + j < n;
+      id[j] = live[j] ? __ldcg(union_ids + u0 + j) : 0;
     }
-    int e_r[kCommMaxRanks];
 #pragma unroll
-    for (int r = 0; r < kCommMaxRanks; ++r) e_r[r] = __shfl_sync(0xffffffffu, ent, r);   // 0 for r >= N
-    for (int k = lane; k <= Ke; k += 32) {
-      float acc = 0.f;
-#pragma unroll
-      for (int r = 0; r < kCommMaxRanks; ++r)            // rank order: identical sum on every replica
-        if (e_r[r]) acc += ld_volatile_f(in_rows + (size_t(r) * cv.cap + (e_r[r] - 1)) * pitch + k);
-      if (k < Ke) {
-        const size_t pi = size_t(id) * Ke + k;
-        float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
-        opt_apply(c, acc * inv_n + hyper.l2_reg * p, p, m, v);
-        a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
-      } else {
-        float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
-        opt_apply(c, acc * inv_n + hyper.l2_reg * p, p, m, v);
-        a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
+    for (int j = 0; j < kRows; ++j) {
+      ent[j] = 0;
+      if (live[j] && lane < N) {
+        ent[j] = __ldcg(entry_of + size_t(id[j]) * N + lane);
+        entry_of[size_t(id[j]) * N + lane] = 0;
       }
     }
-    if (lane == 0) touched[id] = 0;
+    // lane l accumulates columns l, l+32 (factor gradients) and, for l == 0, column Ke (first-order gradient)
+    float acc[kRows][kKPL + 1];
+    float p[kRows][kKPL + 1], m[kRows][kKPL + 1], v[kRows][kKPL + 1];
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+#pragma unroll
+      for (int q = 0; q <= kKPL; ++q) acc[j][q] = 0.f;
+#pragma unroll
+      for (int r = 0; r < kCommMaxRanks; ++r) {     // rank order: identical sum on every replica
+        const int e = __shfl_sync(0xffffffffu, ent[j], r);
+        if (e) {
+          const float* row = in_rows + (size_t(r) * cv.cap + (e - 1)) * pitch;
+#pragma unroll
+          for (int q = 0; q < kKPL; ++q)
+            if (lane + 32 * q < Ke) acc[j][q] += __ldcg(row + lane + 32 * q);
+          if (lane == 0) acc[j][kKPL] += __ldcg(row + Ke);
+        }
+      }
+      if (live[j]) {
+#pragma unroll
+        for (int q = 0; q < kKPL; ++q)
+          if (lane + 32 * q < Ke) {
+            const size_t pi = size_t(id[j]) * Ke + lane + 32 * q;
+            p[j][q] = a.fm_v[pi]; m[j][q] = a.v_s0[pi]; v[j][q] = a.v_s1[pi];
+          }
+        if (lane == 0) { p[j][kKPL] = a.fm_w[id[j]]; m[j][kKPL] = a.w_s0[id[j]]; v[j][kKPL] = a.w_s1[id[j]]; }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      if (!live[j]) continue;
+#pragma unroll
+      for (int q = 0; q < kKPL; ++q)
+        if (lane + 32 * q < Ke) {
+          const size_t pi = size_t(id[j]) * Ke + lane + 32 * q;
+          opt_apply(c, acc[j][q] * inv_n + hyper.l2_reg * p[j][q], p[j][q], m[j][q], v[j][q]);
+          a.fm_v[pi] = p[j][q]; a.v_s0[pi] = m[j][q]; a.v_s1[pi] = v[j][q];
+        }
+      if (lane == 0) {
+        opt_apply(c, acc[j][kKPL] * inv_n + hyper.l2_reg * p[j][kKPL], p[j][kKPL], m[j][kKPL], v[j][kKPL]);
+        a.fm_w[id[j]] = p[j][kKPL]; a.w_s0[id[j]] = m[j][kKPL]; a.w_s1[id[j]] = v[j][kKPL];
+        touched[id[j]] = 0;
+      }
+    }
   }
+  stamp(cv, 13);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -277,9 +386,9 @@ int launch_dense_allreduce_opt(const CommView& cv, float* P, float* s0, float* s
 
 int launch_sparse_exchange_apply(const CommView& cv, const SparseArgs& a, int* entry_of, int* touched, int* union_ids,
                                  const OptHyper& h, cudaStream_t stream) {
-  sparse_push_claim_kernel<<<cv.sparse_ctas, kCommThreads, 0, stream>>>(cv, a, entry_of, touched, union_ids);
+  sparse_push_claim_kernel<<<cv.sparse_ctas, kSparseThreads, 0, stream>>>(cv, a, entry_of, touched, union_ids);
   DFM_LAUNCH_CHECK();
-  sparse_merge_apply_kernel<<<cv.sparse_ctas, kCommThreads, 0, stream>>>(cv, a, entry_of, touched, union_ids, h);
+  sparse_merge_apply_kernel<<<cv.sparse_ctas, kSparseThreads, 0, stream>>>(cv, a, entry_of, touched, union_ids, h);
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

@@ -34,6 +34,8 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
     if (dedupe) {                  // == training step: open optimizer step (see StepState::step)
       st->step += 1;
       st->comm_epoch += 1;
+      st->n_unique = 0;            // counted by dedupe, which is queued behind this kernel
+      st->n_union = 0;             // counted by the multi-GPU claim pass
     }
   }
   // the 8 examples of a CTA are one 32-byte sector of fm_part: staged in smem, stored by one thread

@@ -60,6 +60,7 @@ struct Engine {
   size_t symm_bytes = 0;
   bool comm_ready = false;
   int *entry_of = nullptr, *touched = nullptr, *union_ids = nullptr;
+  unsigned long long* comm_dbg = nullptr;
   std::vector<void*> peer_maps;
 
   template <typename T>
@@ -191,18 +192,18 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   const dfm_engine_config& c = E.cfg;
   const MlpShape& sh = E.sh;
   int rc;
-  if (train) {
-    // sparse-gradient bookkeeping runs beside the forward pass; its results are first needed by embed_bwd,
-    // which is queued behind it on the same side stream
-    DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
-    DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
-    DFM_CUDA_CHECK(cudaMemsetAsync(&E.st->n_unique, 0, 2 * sizeof(int), E.side));   // n_unique, sparse_done
-    if ((rc = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side))) return rc;
-  }
   const float* fm_bias = E.t.dense + E.off[sh.L + 1];
+  // embed_fm_fwd opens the step: it also clears the per-step counters (n_unique, n_union, loss_sum)
   if ((rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], sh.pitch[0], E.s_sum, E.fm_part,
                                 c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, train, s)))
     return rc;
+  if (train) {
+    // sparse-gradient bookkeeping runs beside the MLP; its results are first needed by embed_bwd,
+    // which is queued behind it on the same side stream
+    DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
+    if ((rc = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side))) return rc;
+  }
   for (int l = 0; l < sh.L; ++l) {
     LayerParams lp{};
     lp.st = E.st; lp.bias = E.t.dense + E.off[l] + size_t(sh.K[l]) * sh.N[l];
@@ -269,7 +270,6 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   sa.G = E.G; sa.Gw = E.Gw; sa.slot_of = E.slot_of; sa.uniq_ids = E.uniq_ids; sa.st = E.st;
   sa.Ke = c.embedding_size; sa.V = c.feature_size; sa.grad_scale = gscale;
   if (E.comm_ready) {
-    DFM_CUDA_CHECK(cudaMemsetAsync(&E.st->n_union, 0, sizeof(int), s));
     return launch_sparse_exchange_apply(E.cv, sa, E.entry_of, E.touched, E.union_ids, E.hyper, s);
   }
   return launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
@@ -389,8 +389,8 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   cv.world = world; cv.rank = rank;
   cv.cap = E->cfg.batch_max * E->cfg.field_size;
   cv.row_pitch = g_pitch(E->cfg.embedding_size);
-  cv.dense_ctas = 64;
-  cv.sparse_ctas = 148;
+  cv.dense_ctas = 128;
+  cv.sparse_ctas = 132;      // one 1024-thread CTA per SM, with slack: peers' CTAs must all be resident
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
   size_t o = 0;
   const size_t n4 = size_t(round_up(E->n_dense, 4)) + 8;
@@ -414,6 +414,8 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   if ((rc = E->alloc(&E->entry_of, size_t(E->cfg.feature_size) * world))) return rc;
   if ((rc = E->alloc(&E->touched, size_t(E->cfg.feature_size)))) return rc;
   if ((rc = E->alloc(&E->union_ids, size_t(cv.cap) * world))) return rc;
+  if ((rc = E->alloc(&E->comm_dbg, 32))) return rc;
+  cv.dbg = E->comm_dbg;
   DFM_CUDA_CHECK(cudaDeviceSynchronize());
   return DFM_OK;
 }
@@ -541,6 +543,7 @@ extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** pt
   else if (!strcmp(name, "Gw")) { p = E->Gw; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "uniq_ids")) { p = E->uniq_ids; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "slot_of")) { p = E->slot_of; n = E->cfg.feature_size; }
+  else if (!strcmp(name, "comm_dbg")) { p = E->comm_dbg; n = 64; }   /* 32 x u64 phase timestamps, as int32 pairs */
   else if (!strcmp(name, "act")) {
     DFM_REQUIRE(index >= 0 && index <= sh.L, "act index %d out of range", index);
     p = E->act[index]; n = rows * sh.pitch[index];

@@ -216,6 +216,7 @@ struct CommView {
   int row_pitch;      // floats per inbox row (Ke + 1 rounded up to 4)
   int dense_ctas, sparse_ctas;
   size_t off_dP, off_avg, off_flags, off_in_count, off_in_ids, off_in_rows;
+  unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
 };
 
 // launchers (one per translation unit)
