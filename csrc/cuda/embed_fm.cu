@@ -132,21 +132,40 @@ dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, in
               int* __restrict__ uniq_ids) {
   const int total = st->count * F;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  int won = 0, id = 0;
-  if (i < total) {
-    id = __ldg(ids + i);
-    // reference example: the first one that starts inside this CTA's range of pairs
-    const int first = blockIdx.x * blockDim.x;
-    const int ref = ((first + F - 1) / F) * F + (i % F);
-    const bool leave = ref != i && ref < first + int(blockDim.x) && ref < total && __ldg(ids + ref) == id;
-    if (!leave && slot_of[id] == -1 && atomicCAS(&slot_of[id], -1, -2) == -1) won = 1;
-  }
-  // one counter bump per CTA: returning atomics on a single address serialise at ~50 ns each
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ unsigned char ref_has_twin[1024];     // set by threads that leave their claim to the reference thread
   __shared__ int warp_base[32];
   __shared__ int cta_base;
+  ref_has_twin[threadIdx.x] = 0;
+  __syncthreads();
+
+  // reference example: the first one that starts inside this CTA's range of (example, field) pairs
+  const int first = blockIdx.x * blockDim.x;
+  int id = 0;
+  bool leave = false;
+  if (i < total) {
+    id = __ldg(ids + i);
+    const int ref = ((first + F - 1) / F) * F + (i % F);
+    leave = ref != i && ref < first + int(blockDim.x) && ref < total && __ldg(ids + ref) == id;
+    if (leave) ref_has_twin[ref - first] = 1;
+  }
+  __syncthreads();
+
+  int won = 0;
+  if (i < total && !leave) {
+    const int pre = ref_has_twin[threadIdx.x] ? kSlotMulti : 0;    // known duplicate: claim with the flag set
+    int v = slot_of[id];
+    if (v == -1) v = atomicCAS(&slot_of[id], -1, pre);
+    if (v == -1) won = 1;
+    else if (!slot_multi(v)) atomicOr(&slot_of[id], kSlotMulti);   // somebody else holds it: the id repeats
+  } else if (i < total) {
+    // the reference thread claims (with the flag); if another CTA got there first, make sure the flag is set
+    const int v = slot_of[id];
+    if (v != -1 && !slot_multi(v)) atomicOr(&slot_of[id], kSlotMulti);
+  }
+
+  // one counter bump per CTA: returning atomics on a single address serialise at ~50 ns each
   const unsigned winners = __ballot_sync(0xffffffffu, won);
-  const int warp = threadIdx.x >> 5;
   if (lane == 0) warp_base[warp] = __popc(winners);
   __syncthreads();
   if (warp == 0) {
@@ -164,7 +183,7 @@ dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, in
   if (won) {
     const int s = cta_base + warp_base[warp] + __popc(winners & ((1u << lane) - 1u));
     uniq_ids[s] = id;
-    slot_of[id] = s;
+    atomicOr(&slot_of[id], s + 1);       // keeps a multi flag that arrived while the slot was being allocated
   }
 }
 

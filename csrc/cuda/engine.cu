@@ -61,6 +61,7 @@ struct Engine {
   bool comm_ready = false;
   int *entry_of = nullptr, *touched = nullptr, *union_ids = nullptr;
   unsigned long long* comm_dbg = nullptr;
+  unsigned long long* kern_dbg = nullptr;
   std::vector<void*> peer_maps;
 
   template <typename T>
@@ -92,7 +93,7 @@ static int engine_build(Engine& E) {
     sh.keep[l] = c.keep_prob[l] > 0.f ? c.keep_prob[l] : 1.f;
   }
   sh.N[sh.L] = 1;
-  for (int l = 0; l <= sh.L; ++l) sh.pitch[l] = round_up(sh.K[l] + 1, 8);
+  for (int l = 0; l <= sh.L; ++l) sh.pitch[l] = round_up(sh.K[l] + 1, 16);   // rows start on 32-byte boundaries (256-bit stores)
   E.Bpad = round_up(c.batch_max, kTileM);
 
   size_t o = 0;
@@ -128,6 +129,7 @@ static int engine_build(Engine& E) {
   if ((rc = E.alloc(&E.uniq_ids, max_slots))) return rc;
   if ((rc = E.alloc(&E.slot_of, size_t(c.feature_size), 0xFF))) return rc;   // all -1
   if ((rc = E.alloc(&E.st, 1))) return rc;
+  if ((rc = E.alloc(&E.kern_dbg, 512))) return rc;
 
   // ---- kernel attributes ----
   if ((rc = mlp_layer_set_smem())) return rc;
@@ -156,7 +158,11 @@ static int engine_build(Engine& E) {
         base.push_back(WgradItem{l, m0, n0, std::min(256, round_up(ncol - n0, 16)), 0, 0, 0});
   }
   const int k_chunks = ceil_div(int(rows), kChunkK);
-  int ksplit = std::max(1, std::min(k_chunks, 148 / std::max<int>(1, int(base.size()))));
+  // wgrad runs beside embed_bwd (side stream); both kernels need an SM to themselves per CTA (shared
+  // memory), so together they must fit the chip or they take turns and the overlap is lost.
+  const int eb_ctas = ceil_div(c.batch_max, kTileM) * ceil_div(sh.K[0], 256);
+  const int wg_budget = std::max(int(base.size()), 148 - std::min(eb_ctas, 100));
+  int ksplit = std::max(1, std::min(k_chunks, wg_budget / std::max<int>(1, int(base.size()))));
   const int per = ceil_div(k_chunks, ksplit);
   ksplit = ceil_div(k_chunks, per);
   std::vector<WgradItem> items;
@@ -231,7 +237,7 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   bp.w_out = E.t.dense + E.off[E.sh.L];
   bp.dlogit = E.dlogit; bp.st = E.st;
   bp.ids = ids; bp.vals = vals; bp.s_sum = E.s_sum; bp.slot_of = E.slot_of; bp.G = E.G; bp.Gw = E.Gw;
-  bp.F = c.field_size; bp.Ke = c.embedding_size;
+  bp.F = c.field_size; bp.Ke = c.embedding_size; bp.dbg = E.kern_dbg;
   int rc;
   for (int l = E.sh.L - 1; l >= 1; --l) {       // dz_{l-1} = (h_l > 0) * (dz_l W_l^T) / keep_{l-1}
     LayerParams lp{};
@@ -543,6 +549,7 @@ extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** pt
   else if (!strcmp(name, "Gw")) { p = E->Gw; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "uniq_ids")) { p = E->uniq_ids; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "slot_of")) { p = E->slot_of; n = E->cfg.feature_size; }
+  else if (!strcmp(name, "kern_dbg")) { p = E->kern_dbg; n = 1024; }
   else if (!strcmp(name, "comm_dbg")) { p = E->comm_dbg; n = 64; }   /* 32 x u64 phase timestamps, as int32 pairs */
   else if (!strcmp(name, "act")) {
     DFM_REQUIRE(index >= 0 && index <= sh.L, "act index %d out of range", index);

@@ -3,7 +3,7 @@
 //
 // Layout conventions (all row-major):
 //   K[0] = field_size * embedding_size, N[l] = deep_layers[l], K[l+1] = N[l]
-//   act[l]  bf16 [B, pitch[l]]  input of layer l (act[0] = e = v[id]*x), pitch[l] = round_up(K[l]+1, 8);
+//   act[l]  bf16 [B, pitch[l]]  input of layer l (act[0] = e = v[id]*x), pitch[l] = round_up(K[l]+1, 16);
 //           column K[l] is a constant 1.0 so that the weight-gradient GEMM also yields the bias row
 //   dz[l]   bf16 [B, N[l]]      gradient w.r.t. the pre-activation of layer l
 //   dz[L]   bf16 [B, 16]        column 0 = dlogit (out layer has one output; padded to a legal UMMA N)
@@ -46,6 +46,14 @@ struct OptHyper {
 // gradient at column Ke, padded to a whole number of 32-byte sectors so no two rows share a sector
 // (4-byte read-modify-writes of one sector from different warps serialise badly on this part).
 __host__ __device__ inline int g_pitch(int Ke) { return Ke + 8; }
+
+// slot_of[id] encoding: -1 = id not in the batch; otherwise bits 0..29 = slot + 1 (0 while the claimer is
+// still allocating), bit 30 = the id occurs more than once in the batch (its gradient rows must be
+// combined with atomics; an id that occurs once gets a plain store).
+constexpr int kSlotMulti = 1 << 30;
+constexpr int kSlotMask = kSlotMulti - 1;
+__host__ __device__ inline int slot_index(int v) { return v < 0 ? -1 : (v & kSlotMask) - 1; }
+__host__ __device__ inline bool slot_multi(int v) { return (v & kSlotMulti) != 0; }
 
 struct MlpShape {
   int L;                       // hidden layers
@@ -143,6 +151,7 @@ struct BwdParams {
   float* G;                    // [slots, Ke]
   float* Gw;                   // [slots]
   int F, Ke;
+  unsigned long long* dbg;     // optional phase timestamps (globaltimer ns) written by CTA (0,0)
 };
 
 struct WgradItem {

@@ -25,6 +25,15 @@ constexpr int kEbMaxFields = 16;                   // fields per slab = 256 / Ke
 
 __host__ __device__ inline int eb_s_row_bytes(int Ke) { return Ke * 4 + 16; }
 
+__device__ __forceinline__ void eb_stamp(const BwdParams& p, int slot) {
+  if (p.dbg && (threadIdx.x & 31) == 0 && (blockIdx.y == 0 || blockIdx.y == 3)) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    if (blockIdx.x == 0 && blockIdx.y == 0) p.dbg[slot] = t;
+    if (blockIdx.y == 3) p.dbg[200 + blockIdx.x * 8 + slot] = t;
+  }
+}
+
 __global__ void __launch_bounds__(kBwdThreads, 1)
 embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ BwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -41,12 +50,19 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) eb_stamp(p, 0);
+  if (threadIdx.x == 0 && p.dbg) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); p.dbg[8 + 2 * (blockIdx.y * gridDim.x + blockIdx.x)] = t; }
   const int m0 = blockIdx.x * kTileM;
-  const int n0 = blockIdx.y * 256;                 // first column of this slab of de [B, K0]
+  // A slab is four 64-column boxes of de [B, K0] taken with stride gridDim.y, not four adjacent ones:
+  // the numeric Criteo fields come first and need ~1/3 of the atomics of a categorical field, so
+  // adjacent boxes would give a few CTAs all the cheap fields and the rest all the expensive ones.
+  // Local column c (0..255) is global column gcol(c).
+  const int n_slabs = gridDim.y;
+  auto gcol = [&](int c) { return ((int(blockIdx.y) + n_slabs * (c >> 6)) << 6) + (c & 63); };
   const int count = p.st->count;
   if (m0 >= count) return;
   const int K0 = p.sh.K[0], N0 = p.sh.N[0];
-  const int n_here = min(256, ((K0 - n0) + 15) & ~15);
+  const int n_here = 256;                          // boxes past K0 are zero-filled by TMA and skipped below
   const int num_kc = cdiv(N0, kChunkK);
 
   if (warp == 0 && lane == 0) {
@@ -64,6 +80,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) eb_stamp(p, 1);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -76,7 +93,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         tma_load_2d(a_dst, &maps.dz[0], &full_bar[s], kc * kChunkK, m0);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          tma_load_2d(a_dst + 16384 + j * 8192, &maps.w[0], &full_bar[s], kc * kChunkK, n0 + 64 * j);
+          tma_load_2d(a_dst + 16384 + j * 8192, &maps.w[0], &full_bar[s], kc * kChunkK, gcol(64 * j));
       }
     }
   } else if (warp == 1) {
@@ -95,6 +112,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         umma_commit(&empty_bar[s]);
       }
       umma_commit(acc_bar);
+      eb_stamp(p, 2);
     }
   } else {
     const int q = warp & 3;
@@ -104,24 +122,36 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
     const uint32_t t_row = tmem_base + (uint32_t(q * 32) << 16);
     const float dl = valid ? __ldg(p.dlogit + b) : 0.f;
     const bool all_valid = __all_sync(0xffffffffu, valid);
-    const int f_first = n0 / Ke;
-    const int nf = min(kEbMaxFields, (n_here + Ke - 1) / Ke);
+    const int fpb = 64 / Ke;                        // fields per box (Ke is 16, 32 or 64)
+    const int nf = 4 * fpb;                         // metadata slot j <-> field of local column j * Ke
 
     // ---- while the MMAs run: stage everything the epilogue needs, with all loads in flight at once ----
-    // (1) per-(example, field) metadata: slot of the id, feature value
-    for (int j = 0; j < nf; ++j) {
-      int slot = 0;
-      float x = 0.f;
-      if (valid && f_first + j < F) {
-        x = __ldg(p.vals + size_t(b) * F + f_first + j);
-        slot = p.slot_of[__ldg(p.ids + size_t(b) * F + f_first + j)];
+    // (1) per-(example, field) metadata: slot of the id, feature value.  Three passes so that the loads of
+    //     all fields are in flight together (ids -> slots is a dependent chain; one field at a time costs
+    //     two memory latencies per field).
+    {
+      int idv[kEbMaxFields];
+      float xv[kEbMaxFields];
+#pragma unroll
+      for (int j = 0; j < kEbMaxFields; ++j) {
+        const int f = gcol(j * Ke) / Ke;
+        const bool on = valid && j < nf && f < F;
+        idv[j] = on ? __ldg(p.ids + size_t(b) * F + f) : -1;
+        xv[j] = on ? __ldg(p.vals + size_t(b) * F + f) : 0.f;
       }
-      meta[row * kEbMaxFields + j] = make_int2(slot, __float_as_int(x));
+      int sl[kEbMaxFields];
+#pragma unroll
+      for (int j = 0; j < kEbMaxFields; ++j) sl[j] = idv[j] >= 0 ? p.slot_of[idv[j]] : 0;   // encoded: see slot_index()
+#pragma unroll
+      for (int j = 0; j < kEbMaxFields; ++j)
+        if (j < nf) meta[row * kEbMaxFields + j] = make_int2(sl[j], __float_as_int(xv[j]));
     }
     // (2) this warp's 32 rows of the e slab: lane j fetches 16-byte granule j of each row (coalesced)
     {
-      const __nv_bfloat16* e_base = p.act[0] + size_t(m0 + q * 32) * p.sh.pitch[0] + n0;
-      const bool g_ok = n0 + lane * 8 < K0;
+      // lane j fetches 16-byte granule j of the 512-byte local row = 8 columns of box j / 8
+      const int gc = gcol(lane * 8);
+      const __nv_bfloat16* e_base = p.act[0] + size_t(m0 + q * 32) * p.sh.pitch[0] + gc - lane * 8;
+      const bool g_ok = gc < K0;
 #pragma unroll
       for (int r0 = 0; r0 < 32; r0 += 8) {
         uint4 v[8];
@@ -136,39 +166,54 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
           *reinterpret_cast<uint4*>(e_tile + size_t(q * 32 + r0 + i) * kEbRowBytes + lane * 16) = v[i];
       }
     }
-    // (3) this warp's 32 rows of sum_f e (contiguous in memory: rows are Ke floats)
+    // (3) this warp's 32 rows of sum_f e (contiguous in memory: rows are Ke floats), 8 loads in flight
     {
       const float* s_base = p.s_sum + size_t(m0 + q * 32) * Ke;
-      const int total4 = 32 * Ke / 4;
-      for (int i = lane; i < total4; i += 32) {
-        const int e0 = i * 4, r = e0 / Ke, c = e0 - r * Ke;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (m0 + q * 32 + r < count) v = __ldg(reinterpret_cast<const float4*>(s_base) + i);
-        *reinterpret_cast<float4*>(s_tile + size_t(q * 32 + r) * s_row + c * 4) = v;
+      const int total4 = 32 * Ke / 4;                 // multiple of 128 (Ke % 16 == 0)
+      for (int i0 = lane; i0 < total4; i0 += 32 * 8) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = i0 + 32 * u;
+          v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (i < total4 && m0 + q * 32 + (i * 4) / Ke < count) v[u] = __ldg(reinterpret_cast<const float4*>(s_base) + i);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = i0 + 32 * u;
+          if (i < total4) {
+            const int e0 = i * 4, r = e0 / Ke, c = e0 - r * Ke;
+            *reinterpret_cast<float4*>(s_tile + size_t(q * 32 + r) * s_row + c * 4) = v[u];
+          }
+        }
       }
     }
     __syncwarp();
+    if (warp == 2) eb_stamp(p, 3);
 
     mbar_wait(acc_bar, 0, 300);
     tc_fence_after_sync();
+    if (warp == 2) eb_stamp(p, 4);
 
     const uint8_t* my_e = e_tile + size_t(row) * kEbRowBytes;
     const float* my_s = reinterpret_cast<const float*>(s_tile + size_t(row) * s_row);
     int cur_j = -1, slot = 0;
+    bool multi = true;        // this (example, field)'s id occurs elsewhere in the batch too
     float x = 0.f;
     bool uniform = false;     // every lane of the warp maps this field to the same slot
     for (int c0 = 0; c0 < n_here; c0 += 16) {
       uint32_t r[16];
       tmem_ld_x16(t_row + c0, r);
       tmem_ld_wait();
-      if (n0 + c0 >= K0) break;                 // warp-uniform
+      if (gcol(c0) >= K0) continue;             // warp-uniform: an empty box (past the last field)
       // a 16-column group lies inside one field (Ke % 16 == 0, checked by the host)
       const int j = c0 / Ke;
       const int k0 = c0 - j * Ke;
       if (j != cur_j) {
         cur_j = j;
         const int2 mt = meta[row * kEbMaxFields + j];
-        slot = mt.x;
+        slot = slot_index(mt.x);
+        multi = slot_multi(mt.x);
         x = __int_as_float(mt.y);
         const int s0 = __shfl_sync(0xffffffffu, slot, 0);
         uniform = all_valid && __all_sync(0xffffffffu, slot == s0);
@@ -179,7 +224,8 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
           for (int o = 16; o > 0; o >>= 1) gw += __shfl_xor_sync(0xffffffffu, gw, o);
           if (lane == 0) atomicAdd(p.G + size_t(slot) * GP + Ke, gw);
         } else if (valid) {
-          atomicAdd(p.G + size_t(slot) * GP + Ke, gw);
+          if (multi) atomicAdd(p.G + size_t(slot) * GP + Ke, gw);
+          else p.G[size_t(slot) * GP + Ke] = gw;
         }
       }
       float g[16];
@@ -216,17 +262,27 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         if (lane < 16) atomicAdd(p.G + size_t(slot) * GP + k0 + lane, g[0]);
       } else if (valid) {
         float* dst = p.G + size_t(slot) * GP + k0;
-        red_add_v4(dst, g[0], g[1], g[2], g[3]);
-        red_add_v4(dst + 4, g[4], g[5], g[6], g[7]);
-        red_add_v4(dst + 8, g[8], g[9], g[10], g[11]);
-        red_add_v4(dst + 12, g[12], g[13], g[14], g[15]);
+        if (multi) {
+          red_add_v4(dst, g[0], g[1], g[2], g[3]);
+          red_add_v4(dst + 4, g[4], g[5], g[6], g[7]);
+          red_add_v4(dst + 8, g[8], g[9], g[10], g[11]);
+          red_add_v4(dst + 12, g[12], g[13], g[14], g[15]);
+        } else {
+          // the only occurrence of this id in the batch: the row is zero (the optimizer cleared it), a
+          // plain store is the sum -- and costs the LSU a fraction of what four vector REDs do
+          st_global_v8f(dst, g[0], g[1], g[2], g[3], g[4], g[5], g[6], g[7]);
+          st_global_v8f(dst + 8, g[8], g[9], g[10], g[11], g[12], g[13], g[14], g[15]);
+        }
       }
     }
   }
 
+  if (warp == 2) eb_stamp(p, 5);
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 256);
+  if (threadIdx.x == 0) eb_stamp(p, 6);
+  if (threadIdx.x == 0 && p.dbg) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); p.dbg[9 + 2 * (blockIdx.y * gridDim.x + blockIdx.x)] = t; }
 }
 
 // ------------------------------------- host side -------------------------------------------

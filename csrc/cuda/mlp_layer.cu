@@ -160,9 +160,7 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t pk[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) pk[i] = valid ? pack_bf16x2(a[2 * i], a[2 * i + 1]) : 0u;
-        uint4* g = reinterpret_cast<uint4*>(out_row + c0);
-        g[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        g[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        st_global_v8(out_row + c0, pk);      // 16 bf16 = one whole sector
       }
     }
   }

@@ -58,25 +58,55 @@ sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
   const int n = a.st->n_unique;
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
-  const int GP = g_pitch(a.Ke);
-  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < n; s += warps) {
-    const int id = a.uniq_ids[s];
-    float* grow = a.G + size_t(s) * GP;
-    for (int k = lane; k < a.Ke; k += 32) {
-      const size_t pi = size_t(id) * a.Ke + k;
-      float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
-      const float g = grow[k] * a.grad_scale + hyper.l2_reg * p;
-      grow[k] = 0.f;
-      opt_apply(c, g, p, m, v);
-      a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
+  const int Ke = a.Ke, GP = g_pitch(a.Ke);
+  // One warp per touched row; a row is a chain of dependent loads (id -> table row), so each warp keeps
+  // kRows rows in flight: every stage is issued for all of them before any result is used.
+  constexpr int kRows = 2;
+  constexpr int kKPL = 2;                               // embedding components per lane (Ke <= 64)
+  for (int s0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kRows; s0 < n; s0 += warps * kRows) {
+    int id[kRows];
+    bool live[kRows];
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      live[j] = s0 + j < n;
+      id[j] = live[j] ? a.uniq_ids[s0 + j] : 0;
     }
-    if (lane == 0) {
-      float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
-      const float g = grow[a.Ke] * a.grad_scale + hyper.l2_reg * p;    // first-order gradient rides in the row
-      grow[a.Ke] = 0.f;
-      opt_apply(c, g, p, m, v);
-      a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
-      a.slot_of[id] = -1;
+    // lane l owns columns l, l+32 of the factor row and, for l == 0, the first-order weight (column Ke of G)
+    float g[kRows][kKPL + 1], p[kRows][kKPL + 1], m[kRows][kKPL + 1], v[kRows][kKPL + 1];
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      if (!live[j]) continue;
+      float* grow = a.G + size_t(s0 + j) * GP;
+#pragma unroll
+      for (int q = 0; q < kKPL; ++q)
+        if (lane + 32 * q < Ke) {
+          const size_t pi = size_t(id[j]) * Ke + lane + 32 * q;
+          g[j][q] = grow[lane + 32 * q];
+          p[j][q] = a.fm_v[pi]; m[j][q] = a.v_s0[pi]; v[j][q] = a.v_s1[pi];
+        }
+      if (lane == 0) {
+        g[j][kKPL] = grow[Ke];
+        p[j][kKPL] = a.fm_w[id[j]]; m[j][kKPL] = a.w_s0[id[j]]; v[j][kKPL] = a.w_s1[id[j]];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      if (!live[j]) continue;
+      float* grow = a.G + size_t(s0 + j) * GP;
+#pragma unroll
+      for (int q = 0; q < kKPL; ++q)
+        if (lane + 32 * q < Ke) {
+          const size_t pi = size_t(id[j]) * Ke + lane + 32 * q;
+          grow[lane + 32 * q] = 0.f;
+          opt_apply(c, g[j][q] * a.grad_scale + hyper.l2_reg * p[j][q], p[j][q], m[j][q], v[j][q]);
+          a.fm_v[pi] = p[j][q]; a.v_s0[pi] = m[j][q]; a.v_s1[pi] = v[j][q];
+        }
+      if (lane == 0) {
+        grow[Ke] = 0.f;
+        opt_apply(c, g[j][kKPL] * a.grad_scale + hyper.l2_reg * p[j][kKPL], p[j][kKPL], m[j][kKPL], v[j][kKPL]);
+        a.fm_w[id[j]] = p[j][kKPL]; a.w_s0[id[j]] = m[j][kKPL]; a.w_s1[id[j]] = v[j][kKPL];
+        a.slot_of[id[j]] = -1;
+      }
     }
   }
 }
@@ -88,7 +118,7 @@ table_dense_kernel(const SparseArgs a, const OptHyper hyper) {
   const int lane = threadIdx.x & 31;
   const long long warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   for (long long id = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; id < a.V; id += warps) {
-    const int s = a.slot_of[id];
+    const int s = slot_index(a.slot_of[id]);   // -1 when the id is not in the batch (slot_index(-1) < 0)
     for (int k = lane; k < a.Ke; k += 32) {
       const size_t pi = size_t(id) * a.Ke + k;
       float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
@@ -175,7 +205,7 @@ int launch_sparse_apply(const SparseArgs& a, const OptHyper& h, int max_rows, bo
     const int grid = int(std::min<long long>(148 * 8, (warps_needed + 7) / 8));
     table_dense_kernel<<<grid, 256, 0, stream>>>(a, h);
   } else {
-    const int grid = std::max(1, std::min(148 * 4, ceil_div(max_rows, 8)));
+    const int grid = std::max(1, std::min(148 * 8, ceil_div(max_rows, 16)));
     sparse_apply_kernel<<<grid, 256, 0, stream>>>(a, h);
   }
   DFM_LAUNCH_CHECK();

@@ -221,6 +221,21 @@ __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t granule)
   return row * 128u + ((granule ^ (row & 7u)) << 4);
 }
 
+// 256-bit global stores (sm_100+): one full 32-byte sector per lane.  Lanes of one instruction that each
+// write only 16 bytes of different sectors leave L2 with partial-sector writes, which it handles far
+// more slowly than whole sectors.  `addr` must be 32-byte aligned.
+__device__ __forceinline__ void st_global_v8(void* addr, const uint32_t (&v)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(addr), "r"(v[0]), "r"(v[1]),
+               "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+__device__ __forceinline__ void st_global_v8f(float* addr, float a, float b, float c, float d, float e, float f,
+                                              float g, float h) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d), "f"(e), "f"(f), "f"(g), "f"(h)
+               : "memory");
+}
+
 // Vectorised fp32 reduction into global memory (sm_90+).
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),

@@ -19,7 +19,7 @@ __global__ void __launch_bounds__(256)
 unique_lookup_kernel(const int* __restrict__ ids, int n, const int* __restrict__ slot_of,
                      int* __restrict__ pos_slot) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) pos_slot[i] = slot_of[__ldg(ids + i)];
+  if (i < n) pos_slot[i] = slot_index(slot_of[__ldg(ids + i)]);
 }
 
 // restores the map and publishes the count; one thread per distinct id

@@ -391,13 +391,18 @@ def run_ps(flags, env) -> int:
                 break
         loader.close()
         if chief:
-            # a finished worker never blocks the others (README.md:37); the master waits for them before the last save
-            client.broadcast_simple(OP_DONE)
-            while client.ask(OP_N_DONE) < n_workers:
+            # a finished worker never blocks the others (README.md:37); the master waits for them, then does the
+            # last save / evaluation / export while the parameter servers are still up, and only then lets go
+            while client.ask(OP_N_DONE) < n_workers - 1:
                 time.sleep(0.05)
-            # the PS tasks have left their loops once all workers are done: take the snapshot before that
-        else:
-            client.broadcast_simple(OP_DONE)
+            if ckpt.model_dir:
+                print(tag, "Saving checkpoints for", worker.global_step, "into", ckpt.save(worker.global_step, snapshot()), flush=True)
+            if va:
+                print(tag, "eval:", evaluate(va), flush=True)
+            if flags.servable_model_dir:
+                worker.pull_all()
+                print(tag, "servable model exported to", export_servable(worker.model, flags.servable_model_dir), flush=True)
+        client.broadcast_simple(OP_DONE)
     elif flags.task_type == "eval" and chief:
         print(tag, "eval:", evaluate(va), flush=True)
 

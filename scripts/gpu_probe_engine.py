@@ -39,14 +39,14 @@ def run(B, layers, Ke=32, F=39, V=5000, opt="GD", lr=1.0, l2=0.0, mode="lazy", t
     with torch.no_grad():
         y_w, y_v, e = m.fm_terms(ids, vals)
         h = e.reshape(B, -1)
-        print("e        ", rel(eng.buffer("act", 0, "bf16").view(-1, (eng.K[0] + 1 + 7) // 8 * 8)[:B, :eng.K[0]], h))
+        print("e        ", rel(eng.buffer("act", 0, "bf16").view(-1, (eng.K[0] + 1 + 15) // 16 * 16)[:B, :eng.K[0]], h))
         print("fm_part  ", rel(eng.buffer("fm_part")[:B], m.fm_bias + y_w + y_v))
         print("s_sum    ", rel(eng.buffer("s_sum").view(-1, Ke)[:B], e.sum(1)))
         hs = [h]
         for l in range(len(layers)):
             h = torch.relu(h.bfloat16().float() @ m.mlp_w[l].bfloat16().float() + m.mlp_b[l])
             hs.append(h)
-            pitch = (eng.K[l + 1] + 1 + 7) // 8 * 8
+            pitch = (eng.K[l + 1] + 1 + 15) // 16 * 16
             got = eng.buffer("act", l + 1, "bf16").view(-1, pitch)[:B, :layers[l]]
             print(f"act[{l+1}]   ", rel(got, h))
         logits = m(ids, vals)

@@ -125,7 +125,7 @@ def test_dropout_masks_and_scaling():
     cfg, m, eng, ids, vals, labels = _setup(512, [256, 128, 64], keep=[0.5, 0.8, 1.0], opt="GD", lr=0.0)
     ids32 = ids.int().contiguous()
     eng.forward(ids32, vals, labels)
-    pitch = (256 + 1 + 7) // 8 * 8
+    pitch = (256 + 1 + 15) // 16 * 16
     h_eval = eng.buffer("act", 1, "bf16").view(-1, pitch)[:512, :256].float().clone()
     eng.train_step(ids32, vals, labels)
     h_train = eng.buffer("act", 1, "bf16").view(-1, pitch)[:512, :256].float().clone()
