@@ -59,7 +59,8 @@ struct Engine {
   uint8_t* symm = nullptr;
   size_t symm_bytes = 0;
   bool comm_ready = false;
-  int *entry_of = nullptr, *touched = nullptr, *union_ids = nullptr;
+  unsigned long long* entry_of = nullptr;     // [V, world] {epoch, row+1} of the record rank r sent for an id
+  unsigned int* grid_bar = nullptr;
   unsigned long long* comm_dbg = nullptr;
   unsigned long long* kern_dbg = nullptr;
   std::vector<void*> peer_maps;
@@ -260,14 +261,10 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   wp.items = E.items; wp.st = E.st; wp.part_stride = E.part_stride;
   if ((rc = launch_wgrad(E.wmaps, wp, E.n_items, s))) return rc;
   const float gscale = 1.f;
-  if (E.comm_ready) {
-    if ((rc = launch_dense_allreduce_opt(E.cv, E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride,
-                                         E.Wb, E.n_dense, E.st, E.hyper, s)))
-      return rc;
-  } else if ((rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride, E.Wb,
-                                    E.n_dense, E.st, E.hyper, gscale, s))) {
+  if (!E.comm_ready &&
+      (rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride, E.Wb, E.n_dense, E.st,
+                             E.hyper, gscale, s)))
     return rc;
-  }
 
   DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
   SparseArgs sa{};
@@ -276,7 +273,11 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   sa.G = E.G; sa.Gw = E.Gw; sa.slot_of = E.slot_of; sa.uniq_ids = E.uniq_ids; sa.st = E.st;
   sa.Ke = c.embedding_size; sa.V = c.feature_size; sa.grad_scale = gscale;
   if (E.comm_ready) {
-    return launch_sparse_exchange_apply(E.cv, sa, E.entry_of, E.touched, E.union_ids, E.hyper, s);
+    // multi-GPU: dense all-reduce + optimizer and the sparse exchange + lazy update in one kernel
+    DenseArgs da{};
+    da.P = E.t.dense; da.s0 = E.t.dense_s0; da.s1 = E.t.dense_s1; da.part = E.dP; da.ksplit = E.ksplit;
+    da.part_stride = E.part_stride; da.Wb = E.Wb; da.n = E.n_dense;
+    return launch_exchange_apply(E.cv, sa, da, E.entry_of, E.grid_bar, E.hyper, s);
   }
   return launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
 }
@@ -348,7 +349,8 @@ extern "C" int dfm_engine_train_step(void* h, const int* ids, const float* vals,
 extern "C" int dfm_engine_launches_per_step(void* h) {
   Engine* E = static_cast<Engine*>(h);
   // dedupe, embed_fwd, L forward layers, loss, L-1 backward layers, embed_bwd, wgrad, dense opt, sparse (1 or 2)
-  return 2 + E->sh.L + 1 + (E->sh.L - 1) + 3 + (E->comm_ready ? 2 : 1);
+  // single GPU: + dense opt + sparse apply; multi GPU: + one exchange kernel
+  return 2 + E->sh.L + 1 + (E->sh.L - 1) + 2 + (E->comm_ready ? 1 : 2);
 }
 
 // ---- phase timing (warm, CUDA events) ----------------------------------------------------------
@@ -395,16 +397,13 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   cv.world = world; cv.rank = rank;
   cv.cap = E->cfg.batch_max * E->cfg.field_size;
   cv.row_pitch = g_pitch(E->cfg.embedding_size);
-  cv.dense_ctas = 128;
-  cv.sparse_ctas = 132;      // one 1024-thread CTA per SM, with slack: peers' CTAs must all be resident
+  cv.ctas = 132;             // one 1024-thread CTA per SM, with slack: every rank's CTAs must all be resident
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
   size_t o = 0;
   const size_t n4 = size_t(round_up(E->n_dense, 4)) + 8;
   cv.off_dP = o;        o = align(o + n4 * 4);
-  cv.off_avg = o;       o = align(o + n4 * 4);
-  cv.off_flags = o;     o = align(o + size_t(3) * world * kCommMaxCtas * 4);
+  cv.off_flags = o;     o = align(o + size_t(world) * kCommMaxCtas * 4);
   cv.off_in_count = o;  o = align(o + size_t(world) * kCommMaxCtas * 4);
-  cv.off_in_ids = o;    o = align(o + size_t(world) * cv.cap * 4);
   cv.off_in_rows = o;   o = align(o + size_t(world) * cv.cap * cv.row_pitch * 4);
   E->symm_bytes = o;
   void* p = nullptr;
@@ -418,8 +417,7 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   memcpy(ipc_handle_out, &hd, 64);
   int rc;
   if ((rc = E->alloc(&E->entry_of, size_t(E->cfg.feature_size) * world))) return rc;
-  if ((rc = E->alloc(&E->touched, size_t(E->cfg.feature_size)))) return rc;
-  if ((rc = E->alloc(&E->union_ids, size_t(cv.cap) * world))) return rc;
+  if ((rc = E->alloc(&E->grid_bar, 64))) return rc;
   if ((rc = E->alloc(&E->comm_dbg, 32))) return rc;
   cv.dbg = E->comm_dbg;
   DFM_CUDA_CHECK(cudaDeviceSynchronize());

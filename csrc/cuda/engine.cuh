@@ -223,15 +223,20 @@ struct CommView {
   int world, rank;
   int cap;            // inbox rows per sender (= batch_max * field_size)
   int row_pitch;      // floats per inbox row (Ke + 1 rounded up to 4)
-  int dense_ctas, sparse_ctas;
-  size_t off_dP, off_avg, off_flags, off_in_count, off_in_ids, off_in_rows;
+  int ctas;           // grid of the exchange kernel: <= one CTA per SM, all co-resident
+  size_t off_dP, off_flags, off_in_count, off_in_rows;
   unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
 };
 
 // launchers (one per translation unit)
-int launch_dense_allreduce_opt(const CommView&, float*, float*, float*, const float*, int, size_t,
-                               __nv_bfloat16*, int, const StepState*, const OptHyper&, cudaStream_t);
-int launch_sparse_exchange_apply(const CommView&, const SparseArgs&, int*, int*, int*, const OptHyper&, cudaStream_t);
+struct DenseArgs {
+  float* P; float* s0; float* s1;        // flat dense parameters and optimizer slots
+  const float* part; int ksplit; size_t part_stride;   // split-K slices of the dense gradient
+  __nv_bfloat16* Wb;
+  int n;
+};
+int launch_exchange_apply(const CommView&, const SparseArgs&, const DenseArgs&, unsigned long long*, unsigned int*,
+                          const OptHyper&, cudaStream_t);
 int launch_embed_fm_fwd(const int*, const float*, const float*, const float*, const float*, __nv_bfloat16*, int,
                         float*, float*, int, int, int, StepState*, int*, int*, int, cudaStream_t);
 int launch_fill_ones_column(__nv_bfloat16*, int, int, int, cudaStream_t);

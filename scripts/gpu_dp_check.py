@@ -90,10 +90,8 @@ for _ in range(100):
 e1.record(); torch.cuda.synchronize()
 res["fused_us_per_step_B512"] = round(e0.elapsed_time(e1) * 10, 2)
 dbg = fused.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)
-names = {0: "dense.start", 1: "dense.local_sum_done", 2: "dense.barrierA_done", 3: "dense.reduce_done",
-         4: "dense.barrierB_done", 5: "dense.apply_done", 8: "push.start", 9: "push.done", 10: "push.barrier_done",
-         11: "claim.done", 12: "merge.start", 13: "merge.done",
-         16: "barA.synced", 17: "barA.fenced", 18: "barA.flag_stored", 19: "barA.flag_seen", 20: "barA.acquired"}
+names = {0: "start", 1: "local_sum+push_done", 2: "barrier_done", 3: "dense_apply_done", 4: "index_done",
+         5: "grid_barrier_done", 6: "merge_apply_done"}
 t0 = int(dbg[0])
 res["comm_phases_us"] = {names[i]: round((int(dbg[i]) - t0) / 1000.0, 2) for i in sorted(names)}
 # Adam turns tiny bf16 differences of near-zero gradients into full-size steps; GD is the sharp check
