@@ -179,6 +179,11 @@ def main():
     clocks = sampler.stop()
     ms_dev = e0.elapsed_time(e1)
     del dev_pool
+    if os.environ.get("DFM_BENCH_PHASES") and world > 1 and trainer.backend == "fused":
+        # %globaltimer stamps CTA 0 of the exchange kernel left during the last step (ns since its start)
+        dbg = trainer.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)
+        print(f"[rank {rank}] exchange phases us: " +
+              " ".join(f"{(int(dbg[i]) - int(dbg[0])) / 1e3:.1f}" for i in range(7)), file=sys.stderr, flush=True)
 
     # ---------------- end to end: pinned host -> device every step, loss back to host ----------------
     for i in range(W):

@@ -29,6 +29,7 @@
 // CTA b only ever waits for CTA b of the other ranks, every rank launches the same grid in the same
 // stream order, and every spin is bounded by a watchdog that traps instead of hanging.
 #include "engine.cuh"
+#include "ptx.cuh"
 
 namespace dfm {
 
@@ -115,12 +116,15 @@ __device__ __forceinline__ void grid_barrier(const CommView& cv, unsigned int* b
 }
 
 __global__ void __launch_bounds__(kXThreads, 1)
-exchange_apply_kernel(const CommView cv, const SparseArgs a, const DenseArgs d,
+exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, const DenseArgs d,
                       unsigned long long* __restrict__ entry_of, unsigned int* __restrict__ grid_bar,
                       const OptHyper hyper) {
   const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
   const unsigned int epoch = unsigned(a.st->comm_epoch);       // bumped by the first kernel of the step
-  const int N = cv.world, Ke = a.Ke, pitch = cv.row_pitch;
+  const int N = cv.world, Ke = a.Ke;
+  const int wp = cv.row_pitch;                         // 32-bit words per wire record
+  const int hw = Ke / 2;                               // words holding bf16 gradient pairs; then gw (fp32), id
+  const int gp = g_pitch(Ke);                          // floats per row of the local gradient buffer G
   const float inv_n = 1.f / float(N);
   const int lane = threadIdx.x & 31;
   const int wpc = blockDim.x >> 5;
@@ -146,15 +150,25 @@ exchange_apply_kernel(const CommView cv, const SparseArgs a, const DenseArgs d,
     *reinterpret_cast<float4*>(my_dP + 4 * size_t(g)) = acc;
   }
   // ---------------- phase 0b: push my sparse records to every rank ----------------
+  // wire record = wp words: [hw words of bf16 pairs | first-order gradient fp32 | id]; bf16 on the wire halves
+  // the all-gather's NVLink bytes (the accumulation on the receiving side is fp32, in rank order)
   for (int s = warp_g; s < n_mine; s += warps) {
     const int id = a.uniq_ids[s];
-    float* grow = a.G + size_t(s) * pitch;
-    for (int k = lane; k < pitch; k += 32) {
-      float v = 0.f;
-      if (k <= Ke) { v = grow[k]; grow[k] = 0.f; }
-      else if (k == Ke + 1) v = __int_as_float(id);
+    float* grow = a.G + size_t(s) * gp;
+    for (int w = lane; w < hw + 2; w += 32) {
+      uint32_t word;
+      if (w < hw) {
+        const float2 x = *reinterpret_cast<const float2*>(grow + 2 * w);
+        *reinterpret_cast<float2*>(grow + 2 * w) = make_float2(0.f, 0.f);
+        word = pack_bf16x2(x.x, x.y);
+      } else if (w == hw) {
+        word = __float_as_uint(grow[Ke]);
+        grow[Ke] = 0.f;
+      } else {
+        word = uint32_t(id);
+      }
       for (int r = 0; r < N; ++r)
-        (reinterpret_cast<float*>(cv.base[r] + cv.off_in_rows) + (size_t(cv.rank) * cv.cap + s) * pitch)[k] = v;
+        (reinterpret_cast<uint32_t*>(cv.base[r] + cv.off_in_rows) + (size_t(cv.rank) * cv.cap + s) * wp)[w] = word;
     }
     if (lane == 0) a.slot_of[id] = -1;
   }
@@ -194,7 +208,7 @@ exchange_apply_kernel(const CommView cv, const SparseArgs a, const DenseArgs d,
   // The records pushed by CTA b of rank r are those with row s = b*wpc + w + j*warps (w < wpc): exactly the
   // rows this CTA's barrier covered.  One thread per record; entries carry the epoch, so stale ones are ignored.
   const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_count);
-  const float* in_rows = reinterpret_cast<const float*>(cv.base[cv.rank] + cv.off_in_rows);
+  const uint32_t* in_rows = reinterpret_cast<const uint32_t*>(cv.base[cv.rank] + cv.off_in_rows);
   const int first_warp = blockIdx.x * wpc;
   for (int r = 0; r < N; ++r) {
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
@@ -202,7 +216,7 @@ exchange_apply_kernel(const CommView cv, const SparseArgs a, const DenseArgs d,
     for (int t = threadIdx.x; t < per_cta; t += blockDim.x) {
       const int s = first_warp + (t % wpc) + (t / wpc) * warps;
       if (s < nr) {
-        const int id = __float_as_int(__ldcg(in_rows + (size_t(r) * cv.cap + s) * pitch + Ke + 1));
+        const int id = int(__ldcg(in_rows + (size_t(r) * cv.cap + s) * wp + hw + 1));
         entry_of[size_t(id) * N + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(s + 1);
       }
     }
@@ -212,69 +226,77 @@ exchange_apply_kernel(const CommView cv, const SparseArgs a, const DenseArgs d,
   stamp(cv, 5);
 
   // ---------------- phase 2: owners merge and apply ----------------
-  // One warp per received record, kRows records in flight per warp (each is a chain of dependent loads).
+  // One warp per received record, kRows records in flight per warp (each is a chain of dependent loads:
+  // id -> {index row, table row} -> senders' records).  Lane l owns columns 2l, 2l+1; lane 0 also owns fm_w.
   constexpr int kRows = 2;
-  constexpr int kKPL = 2;                              // embedding components per lane (Ke <= 64)
+  const bool col_lane = lane < hw;
   for (int r = 0; r < N; ++r) {
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
     for (int s0 = warp_g; s0 < nr; s0 += warps * kRows) {
-      int id[kRows];
-      unsigned mask[kRows];
-      int sidx[kRows];
+      int id[kRows], sidx[kRows];
       bool own[kRows];
 #pragma unroll
       for (int j = 0; j < kRows; ++j) {
         const int s = s0 + j * warps;
-        id[j] = s < nr ? __float_as_int(__ldcg(in_rows + (size_t(r) * cv.cap + s) * pitch + Ke + 1)) : -1;
+        id[j] = s < nr ? int(__ldcg(in_rows + (size_t(r) * cv.cap + s) * wp + hw + 1)) : -1;
       }
+      // index row and (speculatively, it is needed if this record turns out to own the id) the table row
+      float2 p[kRows], m[kRows], v[kRows];
+      float pw[kRows], mw[kRows], vw[kRows];
 #pragma unroll
       for (int j = 0; j < kRows; ++j) {
         sidx[j] = 0;
-        if (id[j] >= 0 && lane < N) {
-          const unsigned long long e = __ldcg(entry_of + size_t(id[j]) * N + lane);
-          if (unsigned(e >> 32) == epoch) sidx[j] = int(unsigned(e));
+        if (id[j] >= 0) {
+          if (lane < N) {
+            const unsigned long long e = __ldcg(entry_of + size_t(id[j]) * N + lane);
+            if (unsigned(e >> 32) == epoch) sidx[j] = int(unsigned(e));
+          }
+          if (col_lane) {
+            const size_t pi = size_t(id[j]) * Ke + 2 * lane;
+            p[j] = *reinterpret_cast<const float2*>(a.fm_v + pi);
+            m[j] = *reinterpret_cast<const float2*>(a.v_s0 + pi);
+            v[j] = *reinterpret_cast<const float2*>(a.v_s1 + pi);
+          }
+          if (lane == 0) { pw[j] = a.fm_w[id[j]]; mw[j] = a.w_s0[id[j]]; vw[j] = a.w_s1[id[j]]; }
         }
-        mask[j] = __ballot_sync(0xffffffffu, sidx[j] != 0);
-        own[j] = id[j] >= 0 && (__ffs(mask[j]) - 1) == r;      // the lowest-ranked sender of this id applies it
       }
-      float acc[kRows][kKPL + 1], p[kRows][kKPL + 1], m[kRows][kKPL + 1], v[kRows][kKPL + 1];
+      float2 acc[kRows];
+      float accw[kRows];
 #pragma unroll
       for (int j = 0; j < kRows; ++j) {
+        const unsigned mask = __ballot_sync(0xffffffffu, sidx[j] != 0);
+        own[j] = id[j] >= 0 && (__ffs(mask) - 1) == r;     // the lowest-ranked sender of this id applies it
+        acc[j] = make_float2(0.f, 0.f);
+        accw[j] = 0.f;
 #pragma unroll
-        for (int q = 0; q <= kKPL; ++q) acc[j][q] = 0.f;
-        if (!own[j]) continue;
-#pragma unroll
-        for (int q = 0; q < kCommMaxRanks; ++q) {        // rank order: identical sum on every replica
+        for (int q = 0; q < kCommMaxRanks; ++q) {           // rank order: identical sum on every replica
           const int e = __shfl_sync(0xffffffffu, sidx[j], q);
-          if (e) {
-            const float* row = in_rows + (size_t(q) * cv.cap + (e - 1)) * pitch;
-#pragma unroll
-            for (int u = 0; u < kKPL; ++u)
-              if (lane + 32 * u < Ke) acc[j][u] += __ldcg(row + lane + 32 * u);
-            if (lane == 0) acc[j][kKPL] += __ldcg(row + Ke);
+          if (own[j] && e) {
+            const uint32_t* row = in_rows + (size_t(q) * cv.cap + (e - 1)) * wp;
+            if (col_lane) {
+              const uint32_t w2 = __ldcg(row + lane);
+              const __nv_bfloat162 b2 = *reinterpret_cast<const __nv_bfloat162*>(&w2);
+              acc[j].x += __low2float(b2);
+              acc[j].y += __high2float(b2);
+            }
+            if (lane == 0) accw[j] += __uint_as_float(__ldcg(row + hw));
           }
         }
-#pragma unroll
-        for (int u = 0; u < kKPL; ++u)
-          if (lane + 32 * u < Ke) {
-            const size_t pi = size_t(id[j]) * Ke + lane + 32 * u;
-            p[j][u] = a.fm_v[pi]; m[j][u] = a.v_s0[pi]; v[j][u] = a.v_s1[pi];
-          }
-        if (lane == 0) { p[j][kKPL] = a.fm_w[id[j]]; m[j][kKPL] = a.w_s0[id[j]]; v[j][kKPL] = a.w_s1[id[j]]; }
       }
 #pragma unroll
       for (int j = 0; j < kRows; ++j) {
         if (!own[j]) continue;
-#pragma unroll
-        for (int u = 0; u < kKPL; ++u)
-          if (lane + 32 * u < Ke) {
-            const size_t pi = size_t(id[j]) * Ke + lane + 32 * u;
-            opt_apply(c, acc[j][u] * inv_n + hyper.l2_reg * p[j][u], p[j][u], m[j][u], v[j][u]);
-            a.fm_v[pi] = p[j][u]; a.v_s0[pi] = m[j][u]; a.v_s1[pi] = v[j][u];
-          }
+        if (col_lane) {
+          const size_t pi = size_t(id[j]) * Ke + 2 * lane;
+          opt_apply(c, acc[j].x * inv_n + hyper.l2_reg * p[j].x, p[j].x, m[j].x, v[j].x);
+          opt_apply(c, acc[j].y * inv_n + hyper.l2_reg * p[j].y, p[j].y, m[j].y, v[j].y);
+          *reinterpret_cast<float2*>(a.fm_v + pi) = p[j];
+          *reinterpret_cast<float2*>(a.v_s0 + pi) = m[j];
+          *reinterpret_cast<float2*>(a.v_s1 + pi) = v[j];
+        }
         if (lane == 0) {
-          opt_apply(c, acc[j][kKPL] * inv_n + hyper.l2_reg * p[j][kKPL], p[j][kKPL], m[j][kKPL], v[j][kKPL]);
-          a.fm_w[id[j]] = p[j][kKPL]; a.w_s0[id[j]] = m[j][kKPL]; a.w_s1[id[j]] = v[j][kKPL];
+          opt_apply(c, accw[j] * inv_n + hyper.l2_reg * pw[j], pw[j], mw[j], vw[j]);
+          a.fm_w[id[j]] = pw[j]; a.w_s0[id[j]] = mw[j]; a.w_s1[id[j]] = vw[j];
         }
       }
     }

@@ -222,7 +222,7 @@ struct CommView {
   uint8_t* base[kCommMaxRanks];
   int world, rank;
   int cap;            // inbox rows per sender (= batch_max * field_size)
-  int row_pitch;      // floats per inbox row (Ke + 1 rounded up to 4)
+  int row_pitch;      // 32-bit words per inbox record: Ke/2 bf16 pairs, first-order gradient (fp32), id; whole sectors
   int ctas;           // grid of the exchange kernel: <= one CTA per SM, all co-resident
   size_t off_dP, off_flags, off_in_count, off_in_rows;
   unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
