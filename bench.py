@@ -164,21 +164,30 @@ def main():
     # ---------------- device-timed: inputs rotate through a device-resident pool ----------------
     dev_pool = [s[0].to(dev, non_blocking=True) for s in pool]
     torch.cuda.synchronize()
+    P = len(dev_pool)
     for i in range(W):
-        trainer.train_step_device(dev_pool[i % len(dev_pool)])
+        trainer.train_step_device(dev_pool[i % P], dev_pool[(i + 1) % P])
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
-    for i in range(K):
-        trainer.train_step_device(dev_pool[(W + i) % len(dev_pool)])
+    for i in range(K):     # every step copies its batch from the pool (inside the step graph, beside the kernels)
+        trainer.train_step_device(dev_pool[(W + i) % P], dev_pool[(W + i + 1) % P])
     e1.record()
     barrier()
     clocks = sampler.stop()
     ms_dev = e0.elapsed_time(e1)
     del dev_pool
+    if os.environ.get("DFM_BENCH_TIMELINE") and trainer.backend == "fused" and rank == 0:
+        # %globaltimer at the start of CTA 0 of every kernel of the last step (StepState::kstamp)
+        ks = trainer.engine.buffer("state", dtype="i4").clone().cpu()[12:60].view(torch.int64)
+        names = {0: "embed_fwd", 1: "dedupe", 2: "fwd0", 3: "fwd1", 4: "fwd2", 8: "loss", 11: "bwd2", 10: "bwd1",
+                 15: "embed_bwd", 16: "wgrad", 17: "dense_opt", 22: "dense_opt_end", 18: "sparse|exchange",
+                 19: "sparse_end(cta0)"}
+        line = sorted(((int(ks[k]) - int(ks[0])) / 1e3, n) for k, n in names.items() if int(ks[k]) >= int(ks[0]))
+        print("timeline us: " + "  ".join(f"{n}@{t:.1f}" for t, n in line), file=sys.stderr, flush=True)
     if os.environ.get("DFM_BENCH_PHASES") and world > 1 and trainer.backend == "fused":
         # %globaltimer stamps CTA 0 of the exchange kernel left during the last step (ns since its start)
         dbg = trainer.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)
@@ -187,7 +196,7 @@ def main():
 
     # ---------------- end to end: pinned host -> device every step, loss back to host ----------------
     for i in range(W):
-        trainer.train_step_host(pool[i % len(pool)][0])
+        trainer.train_step_host(pool[i % P][0], pool[(i + 1) % P][0])
     trainer.last_loss()
     barrier()
     h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -195,7 +204,8 @@ def main():
     h0.record()
     loss_acc = 0.0
     for i in range(K):
-        trainer.train_step_host(pool[(W + i) % len(pool)][0])
+        # H2D of batch i+1 (pinned -> device) is a node of step i's graph; step 0's own batch was staged by warm-up
+        trainer.train_step_host(pool[(W + i) % P][0], pool[(W + i + 1) % P][0])
         loss_acc += trainer.last_loss()          # D2H read of the previous step's loss (pipelined by one step)
     final_loss = trainer.last_loss(wait_current=True)
     h1.record()

@@ -140,6 +140,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   float* my_dP = reinterpret_cast<float*>(cv.base[cv.rank] + cv.off_dP);
 
   stamp(cv, 0);
+  kstamp(a.st, kStampSparse);
   // ---------------- phase 0a: local sum of the split-K slices ----------------
   for (int g = g_lo + threadIdx.x; g < g_hi; g += blockDim.x) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -302,6 +303,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
     }
   }
   stamp(cv, 6);
+  kstamp(a.st, kStampSparseEnd);
 }
 
 // ------------------------------------------------------------------------------------------------

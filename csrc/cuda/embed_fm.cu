@@ -29,6 +29,7 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kEmbedWarps + warp;
   const int count = st->count;
+  kstamp(st, kStampEmbedFwd);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->loss_sum = 0.f;            // accumulated by the loss kernel of this step
     if (dedupe) {                  // == training step: open optimizer step (see StepState::step)
@@ -124,44 +125,49 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
 
 // Sparse-gradient bookkeeping, off the critical path (runs on the side stream while the forward pass
 // computes): every distinct id of the batch claims a compact slot.  One thread per (example, field).
-// Fields whose id is the same for every example (the numeric Criteo fields) would make the whole grid
-// CAS one slot_of entry; a thread that sees the CTA's first example carry the same id in the same
-// field leaves the claim to that thread, so such an id costs one CAS per CTA.
+//
+// Same-address atomics serialise in L2 at ~50 ns each and, while they queue, hold up unrelated traffic
+// through that slice (the co-running layer's TMA ring slowed 3x).  Criteo ids are Zipf-distributed and the 13
+// numeric fields carry one id for the whole batch, so the kernel first de-duplicates inside the CTA with a
+// shared-memory hash set: only the first thread to insert an id goes to global memory, which bounds the
+// traffic on a hot id to one CAS per CTA.
+constexpr int kDedupeHash = 2048;                    // >= 2x threads per CTA, power of two
+
 __global__ void __launch_bounds__(1024)
 dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, int* __restrict__ slot_of,
               int* __restrict__ uniq_ids) {
   const int total = st->count * F;
+  kstamp(st, kStampDedupe);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __shared__ unsigned char ref_has_twin[1024];     // set by threads that leave their claim to the reference thread
+  __shared__ int tab_id[kDedupeHash];              // -1 = empty
+  __shared__ unsigned char tab_multi[kDedupeHash]; // the id was inserted more than once in this CTA
   __shared__ int warp_base[32];
   __shared__ int cta_base;
-  ref_has_twin[threadIdx.x] = 0;
+  for (int t = threadIdx.x; t < kDedupeHash; t += blockDim.x) { tab_id[t] = -1; tab_multi[t] = 0; }
   __syncthreads();
 
-  // reference example: the first one that starts inside this CTA's range of (example, field) pairs
-  const int first = blockIdx.x * blockDim.x;
-  int id = 0;
-  bool leave = false;
+  int id = 0, h = 0;
+  bool leader = false;
   if (i < total) {
     id = __ldg(ids + i);
-    const int ref = ((first + F - 1) / F) * F + (i % F);
-    leave = ref != i && ref < first + int(blockDim.x) && ref < total && __ldg(ids + ref) == id;
-    if (leave) ref_has_twin[ref - first] = 1;
+    h = int((unsigned(id) * 2654435761u) >> 21) & (kDedupeHash - 1);
+    while (true) {
+      const int prev = atomicCAS(&tab_id[h], -1, id);
+      if (prev == -1) { leader = true; break; }
+      if (prev == id) { tab_multi[h] = 1; break; }
+      h = (h + 1) & (kDedupeHash - 1);
+    }
   }
   __syncthreads();
 
   int won = 0;
-  if (i < total && !leave) {
-    const int pre = ref_has_twin[threadIdx.x] ? kSlotMulti : 0;    // known duplicate: claim with the flag set
+  if (leader) {
+    const int pre = tab_multi[h] ? kSlotMulti : 0;   // known duplicate: claim with the flag set
     int v = slot_of[id];
     if (v == -1) v = atomicCAS(&slot_of[id], -1, pre);
     if (v == -1) won = 1;
-    else if (!slot_multi(v)) atomicOr(&slot_of[id], kSlotMulti);   // somebody else holds it: the id repeats
-  } else if (i < total) {
-    // the reference thread claims (with the flag); if another CTA got there first, make sure the flag is set
-    const int v = slot_of[id];
-    if (v != -1 && !slot_multi(v)) atomicOr(&slot_of[id], kSlotMulti);
+    else if (!slot_multi(v)) atomicOr(&slot_of[id], kSlotMulti);   // another CTA holds it: the id repeats
   }
 
   // one counter bump per CTA: returning atomics on a single address serialise at ~50 ns each

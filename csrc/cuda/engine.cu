@@ -11,6 +11,8 @@
 //
 // It stands in for one session.run(train_op) of the reference's Estimator loop
 // (HVD.py:430-435: forward, autodiff, Adam apply; SURVEY 3.1 hot loop).
+#include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 #include "engine.cuh"
@@ -53,6 +55,18 @@ struct Engine {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_h2d[kPipe] = {nullptr, nullptr}, ev_done[kPipe] = {nullptr, nullptr};
   long long pipe_step = 0;
+  // pipelined flavours of the step graph: beside the kernels that train on slab w, a memcpy node prefetches the
+  // NEXT batch into slab 1-w, and another copies the loss sum into a pinned ring -- no cross-stream events and no
+  // stream-ordered copies between two graph launches (they cost 11-18 us per step, see scripts/gpu_replay_floor.py)
+  enum { kSrcHost = 0, kSrcDevice = 1 };
+  cudaGraph_t pf_graph[kPipe][2] = {{nullptr, nullptr}, {nullptr, nullptr}};   // kept alive: they own the node handles
+  cudaGraphNode_t pf_node[kPipe][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  cudaGraphExec_t pf_exec[kPipe][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+  cudaStream_t pf_stream = nullptr;
+  cudaEvent_t ev_pf_fork = nullptr, ev_pf_join = nullptr, ev_loss = nullptr;
+  uint8_t* dummy_host = nullptr;               // pinned placeholder source used at capture time
+  float* loss_ring = nullptr;                  // pinned [kPipe]
+  const void* staged_src[kPipe] = {nullptr, nullptr};   // what the prefetch node last copied into each slab
 
   // multi-GPU: symmetric block + peer mappings (see comm.cu)
   CommView cv{};
@@ -63,6 +77,7 @@ struct Engine {
   unsigned int* grid_bar = nullptr;
   unsigned long long* comm_dbg = nullptr;
   unsigned long long* kern_dbg = nullptr;
+  int dedupe_after = 0;          // forward layer after which dedupe is forked (-1: right after embed_fwd); DFM_DEDUPE_AFTER
   std::vector<void*> peer_maps;
 
   template <typename T>
@@ -204,19 +219,25 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   if ((rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], sh.pitch[0], E.s_sum, E.fm_part,
                                 c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, train, s)))
     return rc;
-  if (train) {
-    // sparse-gradient bookkeeping runs beside the MLP; its results are first needed by embed_bwd,
-    // which is queued behind it on the same side stream
+  // Sparse-gradient bookkeeping (dedupe) runs on the side stream beside the MLP; its results are first needed by
+  // embed_bwd, which is queued behind it there.  It is forked after layer `dedupe_after` (default 0): next to the
+  // first, widest layer its 80k atomics-heavy threads slowed that layer's TMA ring from ~8 to ~24 us, while the
+  // later layers only occupy 16-32 SMs.
+  auto fork_dedupe = [&]() -> int {
     DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
     DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
-    if ((rc = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side))) return rc;
-  }
+    return launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side);
+  };
+  const int dedupe_after = std::min(E.dedupe_after, sh.L - 1);
+  if (train && dedupe_after < 0 && (rc = fork_dedupe())) return rc;
   for (int l = 0; l < sh.L; ++l) {
     LayerParams lp{};
     lp.st = E.st; lp.bias = E.t.dense + E.off[l] + size_t(sh.K[l]) * sh.N[l];
     lp.out = E.act[l + 1]; lp.out_pitch = sh.pitch[l + 1];
     lp.n_out = sh.N[l]; lp.k_red = sh.K[l]; lp.b_box_rows = 64; lp.layer = l; lp.keep = sh.keep[l]; lp.seed = c.seed;
+    lp.dbg = E.kern_dbg + 384 + 8 * l;            // kern_dbg: [0,328) embed_bwd, [384,480) 8 stamps per layer kernel
     if ((rc = launch_mlp_layer(false, E.fmaps.act[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
+    if (train && l == dedupe_after && (rc = fork_dedupe())) return rc;
   }
   LossParams q{};
   q.st = E.st; q.h_last = E.act[sh.L]; q.h_pitch = sh.pitch[sh.L]; q.n_last = sh.K[sh.L];
@@ -246,6 +267,7 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
     lp.out = E.dz[l - 1]; lp.out_pitch = E.sh.N[l - 1];
     lp.n_out = E.sh.K[l]; lp.k_red = E.sh.N[l]; lp.b_box_rows = 64; lp.layer = l; lp.keep = E.sh.keep[l - 1];
     lp.seed = c.seed;
+    lp.dbg = E.kern_dbg + 384 + 8 * (kMaxLayers + l);
     if ((rc = launch_mlp_layer(true, E.fmaps.dz[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
   }
 
@@ -291,6 +313,7 @@ extern "C" int dfm_engine_create(const dfm_engine_config* cfg, const dfm_engine_
   Engine* E = new Engine();
   E->cfg = *cfg;
   E->t = *tensors;
+  if (const char* v = getenv("DFM_DEDUPE_AFTER")) E->dedupe_after = atoi(v);
   int rc = engine_build(*E);
   if (rc) {
     for (void* p : E->allocs) cudaFree(p);
@@ -315,8 +338,18 @@ extern "C" int dfm_engine_destroy(void* h) {
     if (E->graph[i]) cudaGraphExecDestroy(E->graph[i]);
     if (E->ev_h2d[i]) cudaEventDestroy(E->ev_h2d[i]);
     if (E->ev_done[i]) cudaEventDestroy(E->ev_done[i]);
+    for (int k = 0; k < 2; ++k) {
+      if (E->pf_exec[i][k]) cudaGraphExecDestroy(E->pf_exec[i][k]);
+      if (E->pf_graph[i][k]) cudaGraphDestroy(E->pf_graph[i][k]);
+    }
   }
   if (E->copy_stream) cudaStreamDestroy(E->copy_stream);
+  if (E->pf_stream) cudaStreamDestroy(E->pf_stream);
+  if (E->ev_pf_fork) cudaEventDestroy(E->ev_pf_fork);
+  if (E->ev_pf_join) cudaEventDestroy(E->ev_pf_join);
+  if (E->ev_loss) cudaEventDestroy(E->ev_loss);
+  if (E->dummy_host) cudaFreeHost(E->dummy_host);
+  if (E->loss_ring) cudaFreeHost(E->loss_ring);
   delete E;
   return DFM_OK;
 }
@@ -474,23 +507,134 @@ extern "C" int dfm_engine_capture(void* h, dfm_stream_t s_) {
     }
   }
   if (!E->copy_stream) DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
+  if (!E->pf_stream) {
+    DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&E->pf_stream, cudaStreamNonBlocking));
+    DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_pf_fork, cudaEventDisableTiming));
+    DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_pf_join, cudaEventDisableTiming));
+    DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_loss, cudaEventDisableTiming));
+    DFM_CUDA_CHECK(cudaMallocHost(reinterpret_cast<void**>(&E->dummy_host), E->slab_bytes));
+    DFM_CUDA_CHECK(cudaMallocHost(reinterpret_cast<void**>(&E->loss_ring), Engine::kPipe * sizeof(float)));
+    memset(E->dummy_host, 0, E->slab_bytes);
+    memset(E->loss_ring, 0, Engine::kPipe * sizeof(float));
+  }
   for (int i = 0; i < Engine::kPipe; ++i) {
     if (E->graph[i]) { cudaGraphExecDestroy(E->graph[i]); E->graph[i] = nullptr; }
+    for (int k = 0; k < 2; ++k) {
+      if (E->pf_exec[i][k]) { cudaGraphExecDestroy(E->pf_exec[i][k]); E->pf_exec[i][k] = nullptr; }
+      if (E->pf_graph[i][k]) { cudaGraphDestroy(E->pf_graph[i][k]); E->pf_graph[i][k] = nullptr; }
+    }
+    E->staged_src[i] = nullptr;
     cudaGraph_t g = nullptr;
+    uint8_t* other = E->in_slab[1 - i];
     DFM_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+    // branch 1: prefetch of the next batch into the other slab (source patched before every launch)
+    DFM_CUDA_CHECK(cudaEventRecord(E->ev_pf_fork, s));
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(E->pf_stream, E->ev_pf_fork, 0));
+    DFM_CUDA_CHECK(cudaMemcpyAsync(other, E->dummy_host, E->slab_bytes, cudaMemcpyHostToDevice, E->pf_stream));
     const int* ids = reinterpret_cast<const int*>(E->in_slab[i]);
     const float* vals = reinterpret_cast<const float*>(E->in_slab[i] + E->off_vals);
     const float* labels = reinterpret_cast<const float*>(E->in_slab[i] + E->off_labels);
     int rc = engine_forward(*E, ids, vals, labels, 1, s);
+    // branch 2: the loss sum is final once the loss kernel has run; it leaves for the pinned ring from there
+    DFM_CUDA_CHECK(cudaEventRecord(E->ev_loss, s));
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(E->pf_stream, E->ev_loss, 0));
+    DFM_CUDA_CHECK(cudaMemcpyAsync(E->loss_ring + i, &E->st->loss_sum, sizeof(float), cudaMemcpyDeviceToHost, E->pf_stream));
+    DFM_CUDA_CHECK(cudaEventRecord(E->ev_pf_join, E->pf_stream));
     if (!rc) rc = engine_backward_update(*E, ids, vals, s);
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E->ev_pf_join, 0));
     cudaError_t ce = cudaStreamEndCapture(s, &g);
     if (rc) { if (g) cudaGraphDestroy(g); return rc; }
     if (ce != cudaSuccess) { set_error("cudaStreamEndCapture: %s", cudaGetErrorString(ce)); return DFM_ERR_CUDA; }
-    ce = cudaGraphInstantiate(&E->graph[i], g, 0);
-    cudaGraphDestroy(g);
+
+    // find the prefetch node (the memcpy whose destination is the other slab)
+    size_t n_nodes = 0;
+    DFM_CUDA_CHECK(cudaGraphGetNodes(g, nullptr, &n_nodes));
+    std::vector<cudaGraphNode_t> nodes(n_nodes);
+    DFM_CUDA_CHECK(cudaGraphGetNodes(g, nodes.data(), &n_nodes));
+    cudaGraphNode_t pf = nullptr;
+    for (cudaGraphNode_t nd : nodes) {
+      cudaGraphNodeType ty;
+      DFM_CUDA_CHECK(cudaGraphNodeGetType(nd, &ty));
+      if (ty != cudaGraphNodeTypeMemcpy) continue;
+      cudaMemcpy3DParms mp{};
+      DFM_CUDA_CHECK(cudaGraphMemcpyNodeGetParams(nd, &mp));
+      if (mp.dstPtr.ptr == other) pf = nd;
+    }
+    DFM_REQUIRE(pf != nullptr, "dfm_engine_capture: prefetch node not found in the captured graph");
+
+    // flavour 0: pinned-host source (as captured)
+    E->pf_graph[i][Engine::kSrcHost] = g;
+    E->pf_node[i][Engine::kSrcHost] = pf;
+    DFM_CUDA_CHECK(cudaGraphInstantiate(&E->pf_exec[i][Engine::kSrcHost], g, 0));
+    // flavour 1: device source
+    cudaGraph_t gd = nullptr;
+    cudaGraphNode_t pfd = nullptr;
+    DFM_CUDA_CHECK(cudaGraphClone(&gd, g));
+    DFM_CUDA_CHECK(cudaGraphNodeFindInClone(&pfd, pf, gd));
+    DFM_CUDA_CHECK(cudaGraphMemcpyNodeSetParams1D(pfd, other, E->in_slab[i], E->slab_bytes, cudaMemcpyDeviceToDevice));
+    E->pf_graph[i][Engine::kSrcDevice] = gd;
+    E->pf_node[i][Engine::kSrcDevice] = pfd;
+    DFM_CUDA_CHECK(cudaGraphInstantiate(&E->pf_exec[i][Engine::kSrcDevice], gd, 0));
+    // plain flavour: no prefetch
+    cudaGraph_t gp = nullptr;
+    cudaGraphNode_t pfp = nullptr;
+    DFM_CUDA_CHECK(cudaGraphClone(&gp, g));
+    DFM_CUDA_CHECK(cudaGraphNodeFindInClone(&pfp, pf, gp));
+    DFM_CUDA_CHECK(cudaGraphDestroyNode(pfp));
+    ce = cudaGraphInstantiate(&E->graph[i], gp, 0);
+    cudaGraphDestroy(gp);
     if (ce != cudaSuccess) { set_error("cudaGraphInstantiate: %s", cudaGetErrorString(ce)); return DFM_ERR_CUDA; }
   }
   E->pipe_step = 0;
+  return DFM_OK;
+}
+
+// One pipelined step: trains on `cur` and, beside it, copies `next` (pinned host or device memory, or null)
+// into the other input slab for the following call.  If `cur` is not what the previous call prefetched it is
+// copied first, in stream order (correct, but the copy is then on the critical path).  `*slot` receives the
+// index of the pinned loss-ring entry this step writes (read it after the work queued here has finished).
+extern "C" int dfm_engine_step_pipelined(void* h, const void* cur, const void* next, int* slot, dfm_stream_t s_) {
+  Engine* E = static_cast<Engine*>(h);
+  cudaStream_t s = static_cast<cudaStream_t>(s_);
+  const int w = int(E->pipe_step % Engine::kPipe);
+  DFM_REQUIRE(E->graph[w] != nullptr, "dfm_engine_step_pipelined: capture first");
+  DFM_REQUIRE(cur != nullptr, "dfm_engine_step_pipelined: null batch");
+  if (E->staged_src[w] != cur)
+    DFM_CUDA_CHECK(cudaMemcpyAsync(E->in_slab[w], cur, E->slab_bytes, cudaMemcpyDefault, s));
+  E->staged_src[w] = nullptr;
+  int kind = -1;
+  if (next) {
+    cudaPointerAttributes at{};
+    DFM_CUDA_CHECK(cudaPointerGetAttributes(&at, next));
+    if (at.type == cudaMemoryTypeHost) kind = Engine::kSrcHost;
+    else if (at.type == cudaMemoryTypeDevice) kind = Engine::kSrcDevice;
+  }
+  if (kind < 0) {
+    DFM_CUDA_CHECK(cudaGraphLaunch(E->graph[w], s));
+  } else {
+    DFM_CUDA_CHECK(cudaGraphExecMemcpyNodeSetParams1D(
+        E->pf_exec[w][kind], E->pf_node[w][kind], E->in_slab[1 - w], next, E->slab_bytes,
+        kind == Engine::kSrcHost ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice));
+    DFM_CUDA_CHECK(cudaGraphLaunch(E->pf_exec[w][kind], s));
+    E->staged_src[1 - w] = next;
+  }
+  DFM_CUDA_CHECK(cudaEventRecord(E->ev_done[w], s));
+  if (slot) *slot = w;
+  E->pipe_step++;
+  return DFM_OK;
+}
+
+extern "C" int dfm_engine_reset_pipeline(void* h) {
+  Engine* E = static_cast<Engine*>(h);
+  E->staged_src[0] = E->staged_src[1] = nullptr;
+  return DFM_OK;
+}
+
+extern "C" int dfm_engine_loss_ring(void* h, float** ring, int* n) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(E->loss_ring != nullptr, "dfm_engine_loss_ring: capture first");
+  *ring = E->loss_ring;
+  *n = Engine::kPipe;
   return DFM_OK;
 }
 
@@ -498,6 +642,7 @@ extern "C" int dfm_engine_capture(void* h, dfm_stream_t s_) {
 extern "C" int dfm_engine_replay(void* h, int which, dfm_stream_t s) {
   Engine* E = static_cast<Engine*>(h);
   DFM_REQUIRE(which >= 0 && which < Engine::kPipe && E->graph[which], "dfm_engine_replay: capture first");
+  E->staged_src[0] = E->staged_src[1] = nullptr;
   DFM_CUDA_CHECK(cudaGraphLaunch(E->graph[which], static_cast<cudaStream_t>(s)));
   return DFM_OK;
 }
@@ -509,16 +654,17 @@ extern "C" int dfm_engine_slab_ptr(void* h, int which, void** ptr) {
   return DFM_OK;
 }
 
-// One end-to-end step from pinned host memory: H2D of the batch on the copy stream (overlapping the
-// previous step's kernels), graph replay on `stream`, D2H of the loss sum into `loss_host` (pinned).
+// One end-to-end step from pinned host memory (or from another device buffer: the copy kind is inferred
+// from the pointer): the batch is copied on the copy stream (overlapping the previous step's kernels), graph replay on `stream`, D2H of the loss sum into `loss_host` (pinned).
 extern "C" int dfm_engine_step_from_host(void* h, const void* host_slab, float* loss_host, dfm_stream_t s_) {
   Engine* E = static_cast<Engine*>(h);
   cudaStream_t s = static_cast<cudaStream_t>(s_);
   const int w = int(E->pipe_step % Engine::kPipe);
   DFM_REQUIRE(E->graph[w] != nullptr, "dfm_engine_step_from_host: capture first");
+  E->staged_src[0] = E->staged_src[1] = nullptr;
   // slab w was last read by step (pipe_step - kPipe)
   if (E->pipe_step >= Engine::kPipe) DFM_CUDA_CHECK(cudaStreamWaitEvent(E->copy_stream, E->ev_done[w], 0));
-  DFM_CUDA_CHECK(cudaMemcpyAsync(E->in_slab[w], host_slab, E->slab_bytes, cudaMemcpyHostToDevice, E->copy_stream));
+  DFM_CUDA_CHECK(cudaMemcpyAsync(E->in_slab[w], host_slab, E->slab_bytes, cudaMemcpyDefault, E->copy_stream));
   DFM_CUDA_CHECK(cudaEventRecord(E->ev_h2d[w], E->copy_stream));
   DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E->ev_h2d[w], 0));
   DFM_CUDA_CHECK(cudaGraphLaunch(E->graph[w], s));

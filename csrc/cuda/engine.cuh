@@ -32,7 +32,24 @@ struct StepState {
   int n_union;        // multi-GPU: distinct rows touched by any rank this step
   int comm_epoch;     // multi-GPU: completed collective rounds (flag value of the next round = +1)
   int pad[3];
+  // %globaltimer when CTA 0 of each kernel of the last step started (slots: kStamp*); read by the
+  // timeline probe (scripts/gpu_timeline.py) to see launch gaps inside the replayed graph
+  unsigned long long kstamp[24];
 };
+
+enum : int { kStampEmbedFwd = 0, kStampDedupe = 1, kStampFwd0 = 2, kStampLoss = 8, kStampBwd0 = 9, kStampEmbedBwd = 15,
+             kStampWgrad = 16, kStampDenseOpt = 17, kStampSparse = 18, kStampSparseEnd = 19, kStampEmbedBwdEnd = 20,
+             kStampWgradEnd = 21, kStampDenseEnd = 22, kStampDedupeEnd = 23 };
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void kstamp(const StepState* st, int slot) {
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    const_cast<StepState*>(st)->kstamp[slot] = t;
+  }
+}
+#endif
 
 struct OptHyper {
   int kind;            // DFM_OPT_*
@@ -201,6 +218,7 @@ struct LayerParams {
   int layer;
   float keep;                     // forward: keep_l ; backward: keep_{l-1}
   unsigned long long seed;
+  unsigned long long* dbg;        // optional: 8 phase timestamps of CTA (0,0)
 };
 
 struct LossParams {

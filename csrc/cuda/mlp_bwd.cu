@@ -51,6 +51,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) eb_stamp(p, 0);
+  kstamp(p.st, kStampEmbedBwd);
   if (threadIdx.x == 0 && p.dbg) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); p.dbg[8 + 2 * (blockIdx.y * gridDim.x + blockIdx.x)] = t; }
   const int m0 = blockIdx.x * kTileM;
   // A slab is four 64-column boxes of de [B, K0] taken with stride gridDim.y, not four adjacent ones:

@@ -23,6 +23,16 @@ constexpr int kLayerStages = 6;
 constexpr int kLayerN = 64;
 constexpr uint32_t kLayerStageBytes = 16384u + 8192u;
 
+// phase stamps of CTA (0,0): 0 start, 1 set-up done, 2 first stage landed, 3 MMAs issued, 4 accumulator ready,
+// 5 epilogue done, 6 end
+__device__ __forceinline__ void layer_stamp(const LayerParams& p, int i) {
+  if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.dbg[i] = t;
+  }
+}
+
 template <bool kBackward>
 __global__ void __launch_bounds__(kLayerThreads, 1)
 mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -38,7 +48,9 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int m0 = blockIdx.x * kTileM;
   const int n0 = blockIdx.y * kLayerN;
   const int count = p.st->count;
+  kstamp(p.st, (kBackward ? kStampBwd0 : kStampFwd0) + p.layer);
   if (m0 >= count) return;
+  if (threadIdx.x == 0) layer_stamp(p, 0);
   const int n_here = min(kLayerN, p.n_out - n0);          // multiple of 16
   const int num_kc = (p.k_red + kChunkK - 1) / kChunkK;
 
@@ -60,6 +72,7 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     if (lane == 0) {
+      layer_stamp(p, 1);
       for (int kc = 0; kc < num_kc; ++kc) {
         const int s = kc % kLayerStages;
         mbar_wait(&empty_bar[s], ((kc / kLayerStages) & 1) ^ 1, 100);
@@ -76,6 +89,7 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int kc = 0; kc < num_kc; ++kc) {
         const int s = kc % kLayerStages;
         mbar_wait(&full_bar[s], (kc / kLayerStages) & 1, 200);
+        if (kc == 0) layer_stamp(p, 2);
         tc_fence_after_sync();
         const uint32_t a_addr = smem_u32(smem + size_t(s) * kLayerStageBytes);
         const uint32_t b_addr = a_addr + 16384u;
@@ -90,6 +104,7 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         umma_commit(&empty_bar[s]);
       }
       umma_commit(acc_bar);
+      layer_stamp(p, 3);
     }
   } else {
     const int q = warp & 3;
@@ -121,7 +136,29 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
 
+    // The dropout decisions do not depend on the accumulator either: one Philox4x32-10 call yields eight 16-bit
+    // uniforms, so a row's 64 keep bits cost eight calls, all hidden behind the MMA main loop.
+    uint32_t keep_bits[kLayerN / 32] = {0u, 0u};
+    if (!kBackward && drop) {
+      const uint32_t thr = uint32_t(p.keep * 65536.f);
+#pragma unroll
+      for (int g = 0; g < kLayerN / 8; ++g) {
+        if (8 * g >= n_here) break;
+        uint32_t rnd[4];
+        philox4x32(uint32_t(p.seed), uint32_t(p.seed >> 32), uint32_t(b), uint32_t(p.layer),
+                   uint32_t((n0 >> 3) + g), step, rnd);
+        uint32_t bits = 0u;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          bits |= ((rnd[i] & 0xffffu) < thr ? 1u : 0u) << (2 * i);
+          bits |= ((rnd[i] >> 16) < thr ? 1u : 0u) << (2 * i + 1);
+        }
+        keep_bits[g >> 2] |= bits << (8 * (g & 3));
+      }
+    }
+
     mbar_wait(acc_bar, 0, 300);
+    if (threadIdx.x == 64) layer_stamp(p, 4);
     tc_fence_after_sync();
 #pragma unroll
     for (int c0 = 0; c0 < kLayerN; c0 += 16) {
@@ -134,15 +171,9 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
         for (int i = 0; i < 16; ++i) a[i] = fmaxf(__uint_as_float(r[i]) + bias[c0 + i], 0.f);
         if (drop) {
+          const uint32_t kb = keep_bits[c0 >> 5] >> (c0 & 31);
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint32_t rnd[4];
-            philox4x32(uint32_t(p.seed), uint32_t(p.seed >> 32), uint32_t(b), uint32_t(p.layer),
-                       uint32_t(((n0 + c0) >> 2) + g), step, rnd);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              a[g * 4 + i] = (u32_to_unit(rnd[i]) < p.keep) ? a[g * 4 + i] * inv_keep : 0.f;
-          }
+          for (int i = 0; i < 16; ++i) a[i] = ((kb >> i) & 1u) ? a[i] * inv_keep : 0.f;
         }
       } else {
         const uint4 h0 = hmask[c0 / 8], h1 = hmask[c0 / 8 + 1];
@@ -163,11 +194,13 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         st_global_v8(out_row + c0, pk);      // 16 bf16 = one whole sector
       }
     }
+    if (threadIdx.x == 64) layer_stamp(p, 5);
   }
 
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 64);
+  if (threadIdx.x == 0) layer_stamp(p, 6);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -181,6 +214,7 @@ loss_init_kernel(const LossParams p) {
   const int sub = lane >> 2, part = lane & 3;               // example within the warp, quarter of its row
   const int b = (blockIdx.x * 8 + warp) * 8 + sub;
   const int count = p.st->count;
+  kstamp(p.st, kStampLoss);
   __shared__ float block_loss[8];
   float loss = 0.f;
   const bool valid = b < count;

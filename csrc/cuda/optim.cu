@@ -30,6 +30,7 @@ dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restric
                  __nv_bfloat16* __restrict__ Wb, int n,
                  const StepState* __restrict__ st, const OptHyper hyper, float grad_scale) {
   const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
+  kstamp(st, kStampDenseOpt);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
     float g = 0.f;
     for (int k = 0; k < ksplit; ++k) g += __ldg(part + size_t(k) * part_stride + i);   // fixed order
@@ -44,6 +45,7 @@ dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restric
       P[n - 1] = p2; s0[n - 1] = a2; s1[n - 1] = b2;
     }
   }
+  kstamp(st, kStampDenseEnd);
 }
 
 __global__ void cast_weights_kernel(const float* __restrict__ P, __nv_bfloat16* __restrict__ Wb, int n) {
@@ -56,6 +58,7 @@ __global__ void __launch_bounds__(256)
 sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
   const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
   const int n = a.st->n_unique;
+  kstamp(a.st, kStampSparse);
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const int Ke = a.Ke, GP = g_pitch(a.Ke);
@@ -109,6 +112,7 @@ sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
       }
     }
   }
+  kstamp(a.st, kStampSparseEnd);
 }
 
 // dense_exact: one warp per table row, all rows.

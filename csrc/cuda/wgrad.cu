@@ -28,6 +28,7 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
   uint64_t* empty_bar = full_bar + kWgStages;
   uint64_t* acc_bar = empty_bar + kWgStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+  kstamp(p.st, kStampWgrad);
 
   const WgradItem item = p.items[blockIdx.x];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

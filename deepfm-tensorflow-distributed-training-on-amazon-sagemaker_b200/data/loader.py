@@ -32,6 +32,7 @@ class HostBatch:
     labels: torch.Tensor     # [n]    float32
     count: int
     slab: Optional[torch.Tensor] = None   # the whole slot as bytes: [ids | vals | labels] for batch_size rows
+    slot: Optional[int] = None            # ring slot (only needed with BatchLoader.defer_release)
 
 
 def slab_layout(batch_size: int, field_size: int, ids_dtype: torch.dtype = torch.int32):
@@ -84,6 +85,16 @@ class BatchLoader:
         if not self._h:
             raise DataError(lib.dfio_last_error().decode())
         self._held: Optional[int] = None
+        self.num_slots = num_slots
+        # False: a batch is valid until the next one is requested.  True: the consumer returns every slot itself
+        # with release(slot) -- the trainer does, once the GPU has finished copying the slab (Trainer.train_batches)
+        self.defer_release = False
+
+    def release(self, slot: int) -> None:
+        if self._h is not None:
+            self._lib.dfio_loader_release(self._h, slot)
+        if self._held == slot:
+            self._held = None
 
     def __iter__(self) -> Iterator[HostBatch]:
         return self
@@ -91,9 +102,9 @@ class BatchLoader:
     def __next__(self) -> HostBatch:
         if self._h is None:
             raise StopIteration
-        if self._held is not None:
+        if self._held is not None and not self.defer_release:
             self._lib.dfio_loader_release(self._h, self._held)
-            self._held = None
+        self._held = None
         slot, count = C.c_int(), C.c_int()
         r = self._lib.dfio_loader_next(self._h, C.byref(slot), C.byref(count))
         if r == 0:
@@ -102,7 +113,7 @@ class BatchLoader:
             raise DataError(self._lib.dfio_last_error().decode())
         s, n = slot.value, count.value
         self._held = s
-        return HostBatch(self._ids[s][:n], self._vals[s][:n], self._labels[s][:n], n, self._slabs[s])
+        return HostBatch(self._ids[s][:n], self._vals[s][:n], self._labels[s][:n], n, self._slabs[s], s)
 
     def stats(self):
         r, b, y = C.c_int64(), C.c_int64(), C.c_int64()

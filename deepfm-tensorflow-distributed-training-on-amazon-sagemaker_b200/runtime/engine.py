@@ -152,6 +152,9 @@ class FusedEngine:
         lib.dfm_engine_slab_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
         lib.dfm_engine_replay.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         lib.dfm_engine_step_from_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.dfm_engine_step_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
+        lib.dfm_engine_reset_pipeline.argtypes = [C.c_void_p]
+        lib.dfm_engine_loss_ring.argtypes = [C.c_void_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int)]
         lib._engine_typed = True
 
     def _stream(self) -> C.c_void_p:
@@ -325,6 +328,25 @@ class FusedEngine:
         _native.check(self._lib.dfm_engine_step_from_host(
             self._h, host_slab.data_ptr(), loss_host.data_ptr() if loss_host is not None else None,
             self._stream()), "dfm_engine_step_from_host")
+
+    def step_pipelined(self, cur: torch.Tensor, nxt: Optional[torch.Tensor] = None) -> int:
+        """Trains on slab ``cur`` while the graph's prefetch node copies ``nxt`` (pinned host or device slab)
+        into the other input slab; pass that tensor as ``cur`` next time.  Returns the loss-ring slot."""
+        slot = C.c_int(0)
+        _native.check(self._lib.dfm_engine_step_pipelined(
+            self._h, C.c_void_p(cur.data_ptr()), C.c_void_p(nxt.data_ptr()) if nxt is not None else None,
+            C.byref(slot), self._stream()), "dfm_engine_step_pipelined")
+        return slot.value
+
+    def reset_pipeline(self) -> None:
+        """Forget what the prefetch node staged (call when slab addresses may be reused with new contents)."""
+        _native.check(self._lib.dfm_engine_reset_pipeline(self._h), "dfm_engine_reset_pipeline")
+
+    def loss_ring(self):
+        """ctypes float array over the engine's pinned loss ring (one entry per input slab)."""
+        ptr, n = C.POINTER(C.c_float)(), C.c_int(0)
+        _native.check(self._lib.dfm_engine_loss_ring(self._h, C.byref(ptr), C.byref(n)), "dfm_engine_loss_ring")
+        return (C.c_float * n.value).from_address(C.addressof(ptr.contents))   # a view, not a copy
 
     def launches_per_step(self) -> int:
         return int(self._lib.dfm_engine_launches_per_step(self._h))

@@ -79,10 +79,11 @@ class Trainer:
             if opts.cuda_graph:
                 self.engine.capture(opts.batch_size)
                 self.uses_graph = True
-                self._dev_slab0 = self.engine.device_slab(0)[0]
+                self._eng_loss = self.engine.loss_ring()     # pinned, written by a node of the step graph
             pin = True
             self._loss_ring = [torch.zeros(1, dtype=torch.float32, pin_memory=pin) for _ in range(2)]
             self._loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+            self._loss_src = [None, None]
             self._loss_idx = 0
             self._issued = 0
         else:
@@ -202,21 +203,83 @@ class Trainer:
         else:
             self._eager_step(hb.feat_ids.to(self.device), hb.feat_vals.to(self.device), hb.labels.to(self.device))
 
-    def _after_fused_step(self, host_step: bool = False) -> None:
+    def train_batches(self, loader, limit: Optional[int] = None):
+        """Generator: one optimizer step per batch of ``loader``; yields the batch after its step is queued.
+
+        With the fused back-end and a BatchLoader this is the pipelined path: batch k+1 is fetched before step k is
+        launched and handed to the step graph's prefetch node, and a ring slot goes back to the loader only when
+        the GPU work that reads it has finished (the host may run ``num_slots - 2`` steps ahead)."""
+        from collections import deque
+        B = self.opts.batch_size
+        deferred = self.backend == "fused" and self.uses_graph and hasattr(loader, "defer_release")
+        full = lambda hb: (hb is not None and hb.count == B and hb.slab is not None and hb.slab.is_pinned())
+        pending = deque()          # (event recorded behind the step that read the slot, slot)
+        held = set()               # every ring slot not yet given back
+        it = iter(loader)
+
+        def fetch():
+            hb = next(it, None)
+            if hb is not None and deferred:
+                held.add(hb.slot)
+            return hb
+
+        def give_back(slot):
+            if slot in held:
+                held.discard(slot)
+                loader.release(slot)
+
+        done = 0
+        if deferred:
+            loader.defer_release = True
+            self.engine.reset_pipeline()
+        try:
+            cur = fetch()
+            while cur is not None and (limit is None or done < limit):
+                if deferred:
+                    while len(pending) > max(loader.num_slots - 3, 0):     # leave the parser a free slot
+                        ev, slot = pending.popleft()
+                        ev.synchronize()
+                        give_back(slot)
+                nxt = fetch() if (limit is None or done + 1 < limit) else None
+                if deferred and full(cur):
+                    self.train_step_host(cur.slab, nxt.slab if full(nxt) else None)
+                else:
+                    self.train_batch(cur)
+                if deferred:
+                    ev = torch.cuda.Event()
+                    ev.record(torch.cuda.current_stream(self.device))
+                    pending.append((ev, cur.slot))
+                done += 1
+                yield cur
+                cur = nxt
+        finally:
+            if deferred:
+                torch.cuda.current_stream(self.device).synchronize()
+                for slot in list(held):
+                    give_back(slot)
+                loader.defer_release = False
+                self.engine.reset_pipeline()
+
+    def _after_fused_step(self, graph_slot: Optional[int] = None) -> None:
         i = self._loss_idx
-        if not host_step:
+        if graph_slot is None:
             self._loss_ring[i].copy_(self.engine.loss_sum_tensor(), non_blocking=True)
+        self._loss_src[i] = graph_slot           # None: the trainer's own ring; else: slot of the engine's ring
         self._loss_ev[i].record(torch.cuda.current_stream(self.device))
         self._loss_idx ^= 1
         self._issued += 1
         self.global_step += 1
 
-    def train_step_host(self, host_slab: torch.Tensor) -> None:
-        """Full batch from a pinned host slab ``[ids | vals | labels]`` (see data.loader.alloc_slab)."""
+    def train_step_host(self, host_slab: torch.Tensor, next_slab: Optional[torch.Tensor] = None) -> None:
+        """Full batch from a pinned host slab ``[ids | vals | labels]`` (see data.loader.alloc_slab).
+
+        ``next_slab`` (optional): the batch of the following call.  It is copied to the device by a node of this
+        step's graph, beside the kernels, so no copy and no cross-stream event sits between two graph launches;
+        it must stay unchanged until this step has finished.  The loss must be read (``last_loss``) at least
+        every other step for its value to be that of the expected step (the graph writes a 2-entry ring)."""
         if self.backend == "fused":
             if self.uses_graph:
-                self.engine.step_from_host(host_slab, self._loss_ring[self._loss_idx])
-                self._after_fused_step(host_step=True)
+                self._after_fused_step(self.engine.step_pipelined(host_slab, next_slab))
             else:
                 ids, vals, labels = self._slab_views(host_slab.to(self.device, non_blocking=True))
                 self.engine.train_step(ids, vals, labels)
@@ -225,17 +288,15 @@ class Trainer:
             ids, vals, labels = self._slab_views(host_slab.to(self.device, non_blocking=True))
             self._eager_step(ids, vals, labels)
 
-    def train_step_device(self, dev_slab: torch.Tensor) -> None:
-        """Full batch already on the device (same slab layout)."""
+    def train_step_device(self, dev_slab: torch.Tensor, next_slab: Optional[torch.Tensor] = None) -> None:
+        """Full batch already on the device (same slab layout, same ``next_slab`` contract)."""
         if self.backend == "fused":
             if self.uses_graph:
-                self._dev_slab0.copy_(dev_slab, non_blocking=True)
-                self.engine.replay(0)
+                self._after_fused_step(self.engine.step_pipelined(dev_slab, next_slab))
             else:
                 ids, vals, labels = self._slab_views(dev_slab)
                 self.engine.train_step(ids, vals, labels)
-            self._issued += 1
-            self.global_step += 1
+                self._after_fused_step()
         else:
             ids, vals, labels = self._slab_views(dev_slab)
             self._eager_step(ids, vals, labels)
@@ -254,7 +315,9 @@ class Trainer:
                 return float("nan")
             i = (self._loss_idx ^ 1) if wait_current or self._issued < 2 else self._loss_idx
             self._loss_ev[i].synchronize()
-            return float(self._loss_ring[i][0]) / self.opts.batch_size
+            src = self._loss_src[i]
+            total = float(self._loss_ring[i][0]) if src is None else float(self._eng_loss[src])
+            return total / self.opts.batch_size
         t = self._last_loss_t if wait_current or self._prev_loss_t is None else self._prev_loss_t
         return float(t) if t is not None else float("nan")
 

@@ -125,10 +125,7 @@ def train_epochs(trainer: Trainer, flags: Flags, env: DistEnv, files: Sequence[s
     limit = None if max_batches is None else max_batches * num_epochs
     done = 0
     try:
-        for hb in loader:
-            if limit is not None and done >= limit:
-                break
-            trainer.train_batch(hb)
+        for hb in trainer.train_batches(loader, limit=limit):
             done += 1
             if flags.log_steps > 0 and trainer.global_step % flags.log_steps == 0 and env.is_chief:
                 dt = max(time.time() - t0, 1e-9)

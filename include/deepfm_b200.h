@@ -113,6 +113,15 @@ int dfm_engine_replay(void* engine, int which, dfm_stream_t stream);
 /* One end-to-end step: async H2D of `host_slab` (pinned) on an internal copy stream, graph replay on
  * `stream`, async D2H of the batch loss sum into `loss_host` (pinned, may be NULL). */
 int dfm_engine_step_from_host(void* engine, const void* host_slab, float* loss_host, dfm_stream_t stream);
+/* Pipelined step: trains on `cur` (a full batch slab, pinned host or device memory) and copies `next` (same
+ * kinds, or NULL) into the other input slab beside the kernels, as a node of the same graph; the next call
+ * should then pass that pointer as `cur`.  A `cur` that was not prefetched is copied in stream order first.
+ * `next` must stay unchanged until the work queued by this call has finished.  *slot = entry of the pinned
+ * loss ring (dfm_engine_loss_ring) that receives this step's loss sum. */
+int dfm_engine_step_pipelined(void* engine, const void* cur, const void* next, int* slot, dfm_stream_t stream);
+int dfm_engine_loss_ring(void* engine, float** ring, int* n_slots);
+/* Forget which source pointers are staged (call when slab addresses may be reused with new contents). */
+int dfm_engine_reset_pipeline(void* engine);
 /* Device pointer + element count of an internal buffer:
  * "prob","logit","dlogit","fm_part","s_sum","state","dense_grad","dense_bf16","G","Gw",
  * "uniq_ids","slot_of", and "act"/"dz" with a layer index. */
