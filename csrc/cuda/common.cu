@@ -7,6 +7,15 @@
 
 namespace dfm {
 
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("DFM_PDL");
+    return !(v && v[0] == '0');
+  }();
+  return on;
+}
+
+
 static thread_local char g_err[1024] = "";
 
 void set_error(const char* fmt, ...) {

@@ -86,4 +86,24 @@ __host__ __device__ inline void philox4x32(uint32_t seed_lo, uint32_t seed_hi, u
 // uniform in [0,1)
 __host__ __device__ inline float u32_to_unit(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f); }
 
+// Launch with the programmatic-stream-serialization attribute (programmatic dependent launch): the kernel may be
+// scheduled while the previous kernel of the stream is still running and must call pdl_wait() (ptx.cuh) before it
+// touches anything that kernel wrote.  Inside a stream capture this becomes a programmatic graph edge.
+// DFM_PDL=0 in the environment turns the attribute off (plain stream order).
+bool pdl_enabled();
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 }  // namespace dfm

@@ -12,6 +12,7 @@
 // Outputs: e (bf16, MLP input, row pitch `pitch`), s_sum [B,K] fp32 = sum_f e,
 //          fm_part [B] = fm_bias + y_w + y_v.
 #include "engine.cuh"
+#include "ptx.cuh"
 
 namespace dfm {
 
@@ -29,6 +30,7 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kEmbedWarps + warp;
   const int count = st->count;
+  pdl_launch_dependents();     // the first MLP layer may be scheduled now; it waits for this grid before reading
   kstamp(st, kStampEmbedFwd);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->loss_sum = 0.f;            // accumulated by the loss kernel of this step
@@ -110,6 +112,104 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
   for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
   if (lane == 0) part_out[warp] = tot + __ldg(fm_bias);
   }  // active
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int b0 = blockIdx.x * kEmbedWarps;
+    if (b0 + kEmbedWarps <= count) {
+      float4* dst = reinterpret_cast<float4*>(fm_part + b0);
+      dst[0] = make_float4(part_out[0], part_out[1], part_out[2], part_out[3]);
+      dst[1] = make_float4(part_out[4], part_out[5], part_out[6], part_out[7]);
+    } else {
+      for (int i = 0; b0 + i < count; ++i) fm_part[b0 + i] = part_out[i];
+    }
+  }
+}
+
+// Same pass with Ke/4 lanes per table row (float4 each), so one load instruction of a warp gathers 32/(Ke/4)
+// rows and U of them put U*32/(Ke/4) rows in flight: all 39 fields of a Criteo example in ONE round trip at
+// Ke = 32, where the scalar kernel above needed five dependent rounds of eight.  Used when Ke % 4 == 0.
+template <int U>
+__global__ void __launch_bounds__(kEmbedWarps * 32)
+embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
+                       const float* __restrict__ fm_w, const float* __restrict__ fm_v,
+                       const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
+                       float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
+                       StepState* __restrict__ st, int dedupe) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * kEmbedWarps + warp;
+  const int count = st->count;
+  pdl_launch_dependents();     // the first MLP layer may be scheduled now; it waits for this grid before reading
+  kstamp(st, kStampEmbedFwd);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->loss_sum = 0.f;
+    if (dedupe) {
+      st->step += 1;
+      st->comm_epoch += 1;
+      st->n_unique = 0;
+      st->n_union = 0;
+    }
+  }
+  __shared__ __align__(16) float part_out[kEmbedWarps];
+  const int LPR = Ke >> 2;                 // lanes per row
+  const int G = 32 / LPR;                  // rows per load instruction
+  const int g = lane / LPR, sub = lane - g * LPR;
+  const bool lane_on = g < G;
+  if (b < count) {
+    const int* my_ids = ids + size_t(b) * F;
+    const float* my_vals = vals + size_t(b) * F;
+    float4 S = make_float4(0.f, 0.f, 0.f, 0.f);
+    float acc = 0.f;                       // yw - 0.5 * sum e^2, this lane's share
+    for (int f0 = 0; f0 < F; f0 += G * U) {
+      int id[U];
+      float x[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int f = f0 + u * G + g;
+        const bool on = lane_on && f < F;
+        id[u] = on ? __ldg(my_ids + f) : -1;
+        x[u] = on ? __ldg(my_vals + f) : 0.f;
+      }
+      float4 row[U];
+      float w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        row[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        w[u] = 0.f;
+        if (id[u] >= 0) {
+          row[u] = __ldg(reinterpret_cast<const float4*>(fm_v + size_t(id[u]) * Ke) + sub);
+          if (sub == 0) w[u] = __ldg(fm_w + id[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (id[u] < 0) continue;
+        const int f = f0 + u * G + g;
+        const float4 ev = make_float4(row[u].x * x[u], row[u].y * x[u], row[u].z * x[u], row[u].w * x[u]);
+        S.x += ev.x; S.y += ev.y; S.z += ev.z; S.w += ev.w;
+        acc += w[u] * x[u] - 0.5f * (ev.x * ev.x + ev.y * ev.y + ev.z * ev.z + ev.w * ev.w);
+        uint2 pk;
+        pk.x = pack_bf16x2(ev.x, ev.y);
+        pk.y = pack_bf16x2(ev.z, ev.w);
+        *reinterpret_cast<uint2*>(e + size_t(b) * pitch + size_t(f) * Ke + 4 * sub) = pk;
+      }
+    }
+    // sum S over the G row groups; every lane of group 0 ends with the full sum of its four columns
+    float4 T = S;
+    for (int k = 1; k < G; ++k) {
+      const int src = lane_on ? ((g + k) % G) * LPR + sub : lane;
+      T.x += __shfl_sync(0xffffffffu, S.x, src);
+      T.y += __shfl_sync(0xffffffffu, S.y, src);
+      T.z += __shfl_sync(0xffffffffu, S.z, src);
+      T.w += __shfl_sync(0xffffffffu, S.w, src);
+    }
+    if (lane_on && g == 0) {
+      *reinterpret_cast<float4*>(s_sum + size_t(b) * Ke + 4 * sub) = T;
+      acc += 0.5f * (T.x * T.x + T.y * T.y + T.z * T.z + T.w * T.w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) part_out[warp] = acc + __ldg(fm_bias);
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     const int b0 = blockIdx.x * kEmbedWarps;
@@ -213,6 +313,18 @@ int launch_embed_fm_fwd(const int* ids, const float* vals, const float* fm_w, co
                         int dedupe, cudaStream_t stream) {
   DFM_REQUIRE(Ke <= 32 * kMaxKPerLane, "embedding_size %d > %d is not supported", Ke, 32 * kMaxKPerLane);
   const int grid = ceil_div(batch_max, kEmbedWarps);
+  if (Ke % 4 == 0 && Ke >= 8 && Ke <= 128 && pitch % 4 == 0) {
+    // rows in flight per warp = U * (32 / (Ke/4)); enough to cover F in one round when it fits in registers
+    const int G = 32 / (Ke / 4);
+    if (ceil_div(F, G) <= 10)
+      embed_fm_fwd_v4_kernel<10><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
+                                                                        fm_part, F, Ke, st, dedupe);
+    else
+      embed_fm_fwd_v4_kernel<16><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
+                                                                        fm_part, F, Ke, st, dedupe);
+    DFM_LAUNCH_CHECK();
+    return DFM_OK;
+  }
 #define DFM_EMBED_LAUNCH(KPL)                                                                          \
   embed_fm_fwd_kernel<KPL><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, \
                                                                   s_sum, fm_part, F, Ke, st, slot_of,   \

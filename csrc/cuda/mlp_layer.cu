@@ -47,8 +47,8 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * kTileM;
   const int n0 = blockIdx.y * kLayerN;
-  const int count = p.st->count;
-  kstamp(p.st, (kBackward ? kStampBwd0 : kStampFwd0) + p.layer);
+  const int count = p.st->count;        // set before the step starts, never by a kernel of the step
+  pdl_launch_dependents();
   if (m0 >= count) return;
   if (threadIdx.x == 0) layer_stamp(p, 0);
   const int n_here = min(kLayerN, p.n_out - n0);          // multiple of 16
@@ -69,6 +69,9 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above is CTA-local set-up; from here on the kernel reads what its predecessor wrote
+  pdl_wait();
+  kstamp(p.st, (kBackward ? kStampBwd0 : kStampFwd0) + p.layer);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -214,6 +217,8 @@ loss_init_kernel(const LossParams p) {
   const int sub = lane >> 2, part = lane & 3;               // example within the warp, quarter of its row
   const int b = (blockIdx.x * 8 + warp) * 8 + sub;
   const int count = p.st->count;
+  pdl_launch_dependents();
+  pdl_wait();
   kstamp(p.st, kStampLoss);
   __shared__ float block_loss[8];
   float loss = 0.f;
@@ -296,14 +301,14 @@ int mlp_layer_set_smem() {
 int launch_mlp_layer(bool backward, const CUtensorMap& tmA, const CUtensorMap& tmB, const LayerParams& p,
                      int batch_max, cudaStream_t stream) {
   dim3 grid(ceil_div(batch_max, kTileM), ceil_div(p.n_out, kLayerN));
-  if (backward) mlp_layer_kernel<true><<<grid, kLayerThreads, mlp_layer_smem(), stream>>>(tmA, tmB, p);
-  else          mlp_layer_kernel<false><<<grid, kLayerThreads, mlp_layer_smem(), stream>>>(tmA, tmB, p);
+  if (backward) DFM_CUDA_CHECK(launch_pdl(mlp_layer_kernel<true>, grid, dim3(kLayerThreads), mlp_layer_smem(), stream, tmA, tmB, p));
+  else          DFM_CUDA_CHECK(launch_pdl(mlp_layer_kernel<false>, grid, dim3(kLayerThreads), mlp_layer_smem(), stream, tmA, tmB, p));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }
 
 int launch_loss_init(const LossParams& p, int rows_pad, cudaStream_t stream) {
-  loss_init_kernel<<<ceil_div(rows_pad, 64), 256, 0, stream>>>(p);
+  DFM_CUDA_CHECK(launch_pdl(loss_init_kernel, dim3(ceil_div(rows_pad, 64)), dim3(256), 0, stream, p));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

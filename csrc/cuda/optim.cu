@@ -10,6 +10,7 @@
 //                        which is the math the reference's l2_loss(whole table) implies
 //                        (HVD.py:266-267).
 #include "engine.cuh"
+#include "ptx.cuh"
 
 namespace dfm {
 
@@ -29,6 +30,7 @@ dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restric
                  const float* __restrict__ part, int ksplit, size_t part_stride,
                  __nv_bfloat16* __restrict__ Wb, int n,
                  const StepState* __restrict__ st, const OptHyper hyper, float grad_scale) {
+  pdl_wait();
   const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
   kstamp(st, kStampDenseOpt);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
@@ -192,8 +194,8 @@ int launch_dense_opt(float* P, float* s0, float* s1, const float* part, int kspl
                      __nv_bfloat16* Wb, int n, const StepState* st, const OptHyper& h, float grad_scale,
                      cudaStream_t stream) {
   const int grid = std::min(148 * 8, ceil_div(n, 256));
-  dense_opt_kernel<<<grid, 256, 0, stream>>>(P, s0, s1, part, ksplit, part_stride, Wb, n, st, h, grad_scale);
-  DFM_LAUNCH_CHECK();
+  DFM_CUDA_CHECK(launch_pdl(dense_opt_kernel, dim3(grid), dim3(256), 0, stream, P, s0, s1, part, ksplit, part_stride, Wb, n, st, h,
+                            grad_scale));
   return DFM_OK;
 }
 

@@ -66,6 +66,12 @@ static __device__ __noinline__ void watchdog_trip(int tag) {
   __trap();
 }
 
+// Programmatic dependent launch: a kernel launched with the programmatic-serialization attribute may start while
+// its predecessor in the stream still runs; pdl_wait() blocks until that predecessor has completed and its
+// writes are visible (no-op for a normal launch).  pdl_launch_dependents() lets the successor be scheduled early.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();

@@ -28,7 +28,8 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
   uint64_t* empty_bar = full_bar + kWgStages;
   uint64_t* acc_bar = empty_bar + kWgStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
-  kstamp(p.st, kStampWgrad);
+  // no early pdl_launch_dependents() here: dense_opt's 1184 small CTAs would fill every SM's thread slots while they
+  // wait and keep embed_bwd (other stream) from being scheduled; it is released when this grid's CTAs exit
 
   const WgradItem item = p.items[blockIdx.x];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -36,6 +37,7 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
   const int k_lim = min(item.k_end, (count + 63) & ~63);
   const int l = item.layer;
   if (item.k_begin >= k_lim) {
+    pdl_wait();
     // this batch range is empty (short batch): the slice still has to read as zero
     const int Nl = p.sh.N[l];
     float* base = p.dP[l] + size_t(item.ks) * p.part_stride;
@@ -64,6 +66,8 @@ wgrad_kernel(const __grid_constant__ WgradMaps maps, const __grid_constant__ Wgr
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                              // set-up done; the activations and dz come from the preceding kernels
+  kstamp(p.st, kStampWgrad);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -139,8 +143,7 @@ int wgrad_set_smem() {
 }
 
 int launch_wgrad(const WgradMaps& maps, const WgradParams& prm, int n_items, cudaStream_t stream) {
-  wgrad_kernel<<<n_items, kWgThreads, wgrad_smem(), stream>>>(maps, prm);
-  DFM_LAUNCH_CHECK();
+  DFM_CUDA_CHECK(launch_pdl(wgrad_kernel, dim3(n_items), dim3(kWgThreads), wgrad_smem(), stream, maps, prm));
   return DFM_OK;
 }
 
