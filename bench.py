@@ -188,6 +188,15 @@ def main():
                  19: "sparse_end(cta0)"}
         line = sorted(((int(ks[k]) - int(ks[0])) / 1e3, n) for k, n in names.items() if int(ks[k]) >= int(ks[0]))
         print("timeline us: " + "  ".join(f"{n}@{t:.1f}" for t, n in line), file=sys.stderr, flush=True)
+        kd = trainer.engine.buffer("kern_dbg", dtype="i4").clone().cpu().view(torch.int64)
+        ph = ["start", "setup", "mma_issued", "staged", "acc_ready", "epilogue", "end"]
+        print("embed_bwd CTA(0,0) us: " + "  ".join(f"{ph[i]}@{(int(kd[i]) - int(kd[0])) / 1e3:.1f}" for i in range(7)),
+              file=sys.stderr, flush=True)
+        n_cta = 80
+        st = [int(kd[8 + 2 * i]) for i in range(n_cta)]
+        en = [int(kd[9 + 2 * i]) for i in range(n_cta)]
+        t0 = min(s for s in st if s > 0)
+        print("embed_bwd per-CTA end us: " + " ".join(f"{(e - t0) / 1e3:.0f}" for e in en if e > 0), file=sys.stderr, flush=True)
     if os.environ.get("DFM_BENCH_PHASES") and world > 1 and trainer.backend == "fused":
         # %globaltimer stamps CTA 0 of the exchange kernel left during the last step (ns since its start)
         dbg = trainer.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)

@@ -7,12 +7,12 @@
 
 namespace dfm {
 
-bool pdl_enabled() {
-  static const bool on = [] {
+bool pdl_enabled(int which) {
+  static const int mask = [] {
     const char* v = getenv("DFM_PDL");
-    return !(v && v[0] == '0');
+    return v ? atoi(v) : 0xff;
   }();
-  return on;
+  return (mask & which) != 0;
 }
 
 

@@ -90,10 +90,12 @@ __host__ __device__ inline float u32_to_unit(uint32_t x) { return (x >> 8) * (1.
 // scheduled while the previous kernel of the stream is still running and must call pdl_wait() (ptx.cuh) before it
 // touches anything that kernel wrote.  Inside a stream capture this becomes a programmatic graph edge.
 // DFM_PDL=0 in the environment turns the attribute off (plain stream order).
-bool pdl_enabled();
+// DFM_PDL is a bit mask (default: all): 1 forward layers, 2 loss, 4 backward layers, 8 dense_opt, 16 sparse_apply
+enum : int { kPdlFwd = 1, kPdlLoss = 2, kPdlBwd = 4, kPdlDense = 8, kPdlSparse = 16 };
+bool pdl_enabled(int which);
 #ifdef __CUDACC__
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+inline cudaError_t launch_pdl(int which, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
@@ -101,7 +103,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = pdl_enabled(which) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 #endif

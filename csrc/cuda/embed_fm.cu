@@ -17,6 +17,16 @@
 namespace dfm {
 
 constexpr int kEmbedWarps = 8;
+
+__device__ __forceinline__ void cast_w0(const W0Cast& wc) {
+  const int n2 = wc.n >> 1;                          // src / dst are 8- / 4-byte aligned (checked by the launcher)
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += gridDim.x * blockDim.x) {
+    const float2 v = __ldg(reinterpret_cast<const float2*>(wc.src) + i);
+    reinterpret_cast<uint32_t*>(wc.dst)[i] = pack_bf16x2(v.x, v.y);
+  }
+  if ((wc.n & 1) && blockIdx.x == 0 && threadIdx.x == 0) wc.dst[wc.n - 1] = __float2bfloat16(wc.src[wc.n - 1]);
+}
+
 constexpr int kMaxKPerLane = 4;   // embedding_size <= 128
 
 template <int KPL>   // embedding components per lane: embedding_size <= 32*KPL
@@ -26,12 +36,13 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
                     const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
                     float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
                     StepState* __restrict__ st, int* __restrict__ slot_of, int* __restrict__ uniq_ids,
-                    int dedupe) {
+                    int dedupe, const W0Cast wc) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kEmbedWarps + warp;
   const int count = st->count;
   pdl_launch_dependents();     // the first MLP layer may be scheduled now; it waits for this grid before reading
   kstamp(st, kStampEmbedFwd);
+  cast_w0(wc);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->loss_sum = 0.f;            // accumulated by the loss kernel of this step
     if (dedupe) {                  // == training step: open optimizer step (see StepState::step)
@@ -134,12 +145,13 @@ embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ va
                        const float* __restrict__ fm_w, const float* __restrict__ fm_v,
                        const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
                        float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
-                       StepState* __restrict__ st, int dedupe) {
+                       StepState* __restrict__ st, int dedupe, const W0Cast wc) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kEmbedWarps + warp;
   const int count = st->count;
   pdl_launch_dependents();     // the first MLP layer may be scheduled now; it waits for this grid before reading
   kstamp(st, kStampEmbedFwd);
+  cast_w0(wc);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->loss_sum = 0.f;
     if (dedupe) {
@@ -310,7 +322,9 @@ __global__ void fill_ones_column_kernel(__nv_bfloat16* act, int rows, int pitch,
 int launch_embed_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v,
                         const float* fm_bias, __nv_bfloat16* e, int pitch, float* s_sum, float* fm_part,
                         int F, int Ke, int batch_max, StepState* st, int* slot_of, int* uniq_ids,
-                        int dedupe, cudaStream_t stream) {
+                        int dedupe, W0Cast wc, cudaStream_t stream) {
+  DFM_REQUIRE((reinterpret_cast<uintptr_t>(wc.src) & 7) == 0 && (reinterpret_cast<uintptr_t>(wc.dst) & 3) == 0,
+              "W_0 cast: misaligned buffers");
   DFM_REQUIRE(Ke <= 32 * kMaxKPerLane, "embedding_size %d > %d is not supported", Ke, 32 * kMaxKPerLane);
   const int grid = ceil_div(batch_max, kEmbedWarps);
   if (Ke % 4 == 0 && Ke >= 8 && Ke <= 128 && pitch % 4 == 0) {
@@ -318,17 +332,17 @@ int launch_embed_fm_fwd(const int* ids, const float* vals, const float* fm_w, co
     const int G = 32 / (Ke / 4);
     if (ceil_div(F, G) <= 10)
       embed_fm_fwd_v4_kernel<10><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
-                                                                        fm_part, F, Ke, st, dedupe);
+                                                                        fm_part, F, Ke, st, dedupe, wc);
     else
       embed_fm_fwd_v4_kernel<16><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
-                                                                        fm_part, F, Ke, st, dedupe);
+                                                                        fm_part, F, Ke, st, dedupe, wc);
     DFM_LAUNCH_CHECK();
     return DFM_OK;
   }
 #define DFM_EMBED_LAUNCH(KPL)                                                                          \
   embed_fm_fwd_kernel<KPL><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, \
                                                                   s_sum, fm_part, F, Ke, st, slot_of,   \
-                                                                  uniq_ids, dedupe)
+                                                                  uniq_ids, dedupe, wc)
   if (Ke <= 32) DFM_EMBED_LAUNCH(1);
   else if (Ke <= 64) DFM_EMBED_LAUNCH(2);
   else DFM_EMBED_LAUNCH(4);

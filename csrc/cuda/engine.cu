@@ -45,7 +45,7 @@ struct Engine {
   FwdMaps fmaps; WgradMaps wmaps;
 
   cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork0 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork0 = nullptr, ev_dedupe = nullptr;
 
   // optional: the captured train step and the double-buffered host->device input pipeline
   static constexpr int kPipe = 2;
@@ -200,6 +200,7 @@ static int engine_build(Engine& E) {
   DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_fork, cudaEventDisableTiming));
   DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_join, cudaEventDisableTiming));
   DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_fork0, cudaEventDisableTiming));
+  DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E.ev_dedupe, cudaEventDisableTiming));
 
   StepState init{};
   init.count = c.batch_max; init.step = 0; init.lr = c.lr; init.train = 1;
@@ -217,7 +218,8 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   const float* fm_bias = E.t.dense + E.off[sh.L + 1];
   // embed_fm_fwd opens the step: it also clears the per-step counters (n_unique, n_union, loss_sum)
   if ((rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], sh.pitch[0], E.s_sum, E.fm_part,
-                                c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, train, s)))
+                                c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, train,
+                                W0Cast{E.t.dense + E.off[0], E.Wb + E.off[0], sh.K[0] * sh.N[0]}, s)))
     return rc;
   // Sparse-gradient bookkeeping (dedupe) runs on the side stream beside the MLP; its results are first needed by
   // embed_bwd, which is queued behind it there.  It is forked after layer `dedupe_after` (default 0): next to the
@@ -226,7 +228,10 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   auto fork_dedupe = [&]() -> int {
     DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
     DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
-    return launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side);
+    const int r = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side);
+    if (r) return r;
+    DFM_CUDA_CHECK(cudaEventRecord(E.ev_dedupe, E.side));
+    return DFM_OK;
   };
   const int dedupe_after = std::min(E.dedupe_after, sh.L - 1);
   if (train && dedupe_after < 0 && (rc = fork_dedupe())) return rc;
@@ -271,24 +276,27 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
     if ((rc = launch_mlp_layer(true, E.fmaps.dz[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
   }
 
-  // fork: embedding gradient on the side stream, weight gradients + dense update on the main one
+  // fork: the embedding gradient and the sparse update stay on the main stream (they are the critical path, and a
+  // same-stream kernel->kernel edge is ~2 us cheaper than a cross-stream one); the weight gradients and the dense
+  // update run beside them on the side stream, behind dedupe
   DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork, s));
   DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork, 0));
-  if ((rc = launch_embed_bwd(E.fmaps, bp, c.batch_max, E.side))) return rc;
-  DFM_CUDA_CHECK(cudaEventRecord(E.ev_join, E.side));
+  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_dedupe, 0));
+  if ((rc = launch_embed_bwd(E.fmaps, bp, c.batch_max, s))) return rc;
 
   WgradParams wp{};
   wp.sh = E.sh;
   for (int l = 0; l <= E.sh.L; ++l) wp.dP[l] = E.dP + E.off[l];
   wp.items = E.items; wp.st = E.st; wp.part_stride = E.part_stride;
-  if ((rc = launch_wgrad(E.wmaps, wp, E.n_items, s))) return rc;
+  if ((rc = launch_wgrad(E.wmaps, wp, E.n_items, E.side))) return rc;
   const float gscale = 1.f;
+  // (the dense update leaves the bf16 copy of W_0 alone -- embed_bwd's GEMM may still be reading it; see W0Cast)
   if (!E.comm_ready &&
       (rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride, E.Wb, E.n_dense, E.st,
-                             E.hyper, gscale, s)))
+                             E.hyper, gscale, int(E.off[0]), int(E.off[0]) + E.sh.K[0] * E.sh.N[0], E.side)))
     return rc;
+  DFM_CUDA_CHECK(cudaEventRecord(E.ev_join, E.side));
 
-  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
   SparseArgs sa{};
   sa.fm_v = E.t.fm_v; sa.v_s0 = E.t.fm_v_s0; sa.v_s1 = E.t.fm_v_s1;
   sa.fm_w = E.t.fm_w; sa.w_s0 = E.t.fm_w_s0; sa.w_s1 = E.t.fm_w_s1;
@@ -296,12 +304,15 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   sa.Ke = c.embedding_size; sa.V = c.feature_size; sa.grad_scale = gscale;
   if (E.comm_ready) {
     // multi-GPU: dense all-reduce + optimizer and the sparse exchange + lazy update in one kernel
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
     DenseArgs da{};
     da.P = E.t.dense; da.s0 = E.t.dense_s0; da.s1 = E.t.dense_s1; da.part = E.dP; da.ksplit = E.ksplit;
     da.part_stride = E.part_stride; da.Wb = E.Wb; da.n = E.n_dense;
     return launch_exchange_apply(E.cv, sa, da, E.entry_of, E.grid_bar, E.hyper, s);
   }
-  return launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
+  rc = launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
+  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
+  return rc;
 }
 
 }  // namespace dfm
@@ -334,6 +345,7 @@ extern "C" int dfm_engine_destroy(void* h) {
   if (E->ev_fork) cudaEventDestroy(E->ev_fork);
   if (E->ev_join) cudaEventDestroy(E->ev_join);
   if (E->ev_fork0) cudaEventDestroy(E->ev_fork0);
+  if (E->ev_dedupe) cudaEventDestroy(E->ev_dedupe);
   for (int i = 0; i < Engine::kPipe; ++i) {
     if (E->graph[i]) cudaGraphExecDestroy(E->graph[i]);
     if (E->ev_h2d[i]) cudaEventDestroy(E->ev_h2d[i]);

@@ -255,8 +255,11 @@ struct DenseArgs {
 };
 int launch_exchange_apply(const CommView&, const SparseArgs&, const DenseArgs&, unsigned long long*, unsigned int*,
                           const OptHyper&, cudaStream_t);
+// The bf16 copy of W_0 is refreshed by the FIRST kernel of the next pass (embed_fm_fwd), not by the dense optimizer
+// kernel: that one runs while embed_bwd's GEMM may still be reading W_0 through TMA.
+struct W0Cast { const float* src; __nv_bfloat16* dst; int n; };
 int launch_embed_fm_fwd(const int*, const float*, const float*, const float*, const float*, __nv_bfloat16*, int,
-                        float*, float*, int, int, int, StepState*, int*, int*, int, cudaStream_t);
+                        float*, float*, int, int, int, StepState*, int*, int*, int, W0Cast, cudaStream_t);
 int launch_fill_ones_column(__nv_bfloat16*, int, int, int, cudaStream_t);
 int launch_dedupe(const int*, int, StepState*, int*, int*, int, cudaStream_t);
 int mlp_layer_set_smem();
@@ -268,7 +271,7 @@ int wgrad_set_smem();
 int launch_wgrad(const WgradMaps&, const WgradParams&, int, cudaStream_t);
 int launch_set_state(StepState*, int, float, int, int, cudaStream_t);
 int launch_dense_opt(float*, float*, float*, const float*, int, size_t, __nv_bfloat16*, int, const StepState*,
-                     const OptHyper&, float, cudaStream_t);
+                     const OptHyper&, float, int wb_skip_lo, int wb_skip_hi, cudaStream_t);
 int launch_cast_weights(const float*, __nv_bfloat16*, int, cudaStream_t);
 int launch_sparse_apply(const SparseArgs&, const OptHyper&, int, bool, cudaStream_t);
 

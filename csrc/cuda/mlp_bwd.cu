@@ -12,7 +12,7 @@
 
 namespace dfm {
 
-constexpr int kBwdThreads = 192;
+constexpr int kBwdThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quarter)
 
 
 __device__ __forceinline__ int cdiv(int a, int b) { return (a + b - 1) / b; }
@@ -116,7 +116,11 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
       eb_stamp(p, 2);
     }
   } else {
+    // Two warps share each TMEM lane quarter (a warp may only read lanes 32*(warp%4)..+31): warp pair (q, half)
+    // handles rows 32q..32q+31, local columns [128*half, 128*half+128).  The scatter is bound by how many REDs /
+    // stores the SM has in flight, so eight issuing warps instead of four shorten it.
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     const int b = m0 + row;
     const bool valid = b < count;
@@ -131,21 +135,23 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
     //     all fields are in flight together (ids -> slots is a dependent chain; one field at a time costs
     //     two memory latencies per field).
     {
-      int idv[kEbMaxFields];
-      float xv[kEbMaxFields];
+      int idv[kEbMaxFields / 2];
+      float xv[kEbMaxFields / 2];
+      const int j_lo = half * (nf >> 1);            // the fields of this warp's column half
 #pragma unroll
-      for (int j = 0; j < kEbMaxFields; ++j) {
+      for (int jj = 0; jj < kEbMaxFields / 2; ++jj) {
+        const int j = j_lo + jj;
         const int f = gcol(j * Ke) / Ke;
-        const bool on = valid && j < nf && f < F;
-        idv[j] = on ? __ldg(p.ids + size_t(b) * F + f) : -1;
-        xv[j] = on ? __ldg(p.vals + size_t(b) * F + f) : 0.f;
+        const bool on = valid && jj < (nf >> 1) && f < F;
+        idv[jj] = on ? __ldg(p.ids + size_t(b) * F + f) : -1;
+        xv[jj] = on ? __ldg(p.vals + size_t(b) * F + f) : 0.f;
       }
-      int sl[kEbMaxFields];
+      int sl[kEbMaxFields / 2];
 #pragma unroll
-      for (int j = 0; j < kEbMaxFields; ++j) sl[j] = idv[j] >= 0 ? p.slot_of[idv[j]] : 0;   // encoded: see slot_index()
+      for (int jj = 0; jj < kEbMaxFields / 2; ++jj) sl[jj] = idv[jj] >= 0 ? p.slot_of[idv[jj]] : 0;   // encoded: see slot_index()
 #pragma unroll
-      for (int j = 0; j < kEbMaxFields; ++j)
-        if (j < nf) meta[row * kEbMaxFields + j] = make_int2(sl[j], __float_as_int(xv[j]));
+      for (int jj = 0; jj < kEbMaxFields / 2; ++jj)
+        if (jj < (nf >> 1)) meta[row * kEbMaxFields + j_lo + jj] = make_int2(sl[jj], __float_as_int(xv[jj]));
     }
     // (2) this warp's 32 rows of the e slab: lane j fetches 16-byte granule j of each row (coalesced)
     {
@@ -154,7 +160,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
       const __nv_bfloat16* e_base = p.act[0] + size_t(m0 + q * 32) * p.sh.pitch[0] + gc - lane * 8;
       const bool g_ok = gc < K0;
 #pragma unroll
-      for (int r0 = 0; r0 < 32; r0 += 8) {
+      for (int r0 = 16 * half; r0 < 16 * half + 16; r0 += 8) {     // this warp stages 16 of the quarter's 32 rows
         uint4 v[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -169,27 +175,29 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
     }
     // (3) this warp's 32 rows of sum_f e (contiguous in memory: rows are Ke floats), 8 loads in flight
     {
-      const float* s_base = p.s_sum + size_t(m0 + q * 32) * Ke;
-      const int total4 = 32 * Ke / 4;                 // multiple of 128 (Ke % 16 == 0)
+      const int r_first = q * 32 + 16 * half;         // 16 rows per warp
+      const float* s_base = p.s_sum + size_t(m0 + r_first) * Ke;
+      const int total4 = 16 * Ke / 4;                 // multiple of 64 (Ke % 16 == 0)
       for (int i0 = lane; i0 < total4; i0 += 32 * 8) {
         float4 v[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const int i = i0 + 32 * u;
           v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (i < total4 && m0 + q * 32 + (i * 4) / Ke < count) v[u] = __ldg(reinterpret_cast<const float4*>(s_base) + i);
+          if (i < total4 && m0 + r_first + (i * 4) / Ke < count) v[u] = __ldg(reinterpret_cast<const float4*>(s_base) + i);
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const int i = i0 + 32 * u;
           if (i < total4) {
             const int e0 = i * 4, r = e0 / Ke, c = e0 - r * Ke;
-            *reinterpret_cast<float4*>(s_tile + size_t(q * 32 + r) * s_row + c * 4) = v[u];
+            *reinterpret_cast<float4*>(s_tile + size_t(r_first + r) * s_row + c * 4) = v[u];
           }
         }
       }
     }
-    __syncwarp();
+    // the two warps of a quarter staged half of its rows each
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
     if (warp == 2) eb_stamp(p, 3);
 
     mbar_wait(acc_bar, 0, 300);
@@ -202,7 +210,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
     bool multi = true;        // this (example, field)'s id occurs elsewhere in the batch too
     float x = 0.f;
     bool uniform = false;     // every lane of the warp maps this field to the same slot
-    for (int c0 = 0; c0 < n_here; c0 += 16) {
+    for (int c0 = 128 * half; c0 < 128 * half + 128; c0 += 16) {
       uint32_t r[16];
       tmem_ld_x16(t_row + c0, r);
       tmem_ld_wait();

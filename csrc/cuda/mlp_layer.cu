@@ -9,7 +9,7 @@
 //             A = dz_l [B, N_l]  K-major
 //             B = W_l  rows n0..n0+63 of [K_l, N_l] == K-major UMMA operand
 //
-// Pipeline: warp 0 = TMA producer, warp 1 = TMEM owner + UMMA issuer, warps 2..5 = epilogue; 6-stage
+// Pipeline: warp 0 = TMA producer, warp 1 = TMEM owner + UMMA issuer, warps 2..5 = epilogue; 9-stage
 // smem ring (24 KiB per stage); accumulator 128 lanes x 64 fp32 columns in TMEM.
 // loss_init_kernel closes the forward pass (out layer, sigmoid, BCE) and opens the backward pass
 // (dlogit, dz of the last hidden layer) with one warp per example.
@@ -19,7 +19,7 @@
 namespace dfm {
 
 constexpr int kLayerThreads = 192;
-constexpr int kLayerStages = 6;
+constexpr int kLayerStages = 9;     // 9 x 24 KiB in flight: the first layer's 20-step K loop is latency-bound
 constexpr int kLayerN = 64;
 constexpr uint32_t kLayerStageBytes = 16384u + 8192u;
 
@@ -301,14 +301,14 @@ int mlp_layer_set_smem() {
 int launch_mlp_layer(bool backward, const CUtensorMap& tmA, const CUtensorMap& tmB, const LayerParams& p,
                      int batch_max, cudaStream_t stream) {
   dim3 grid(ceil_div(batch_max, kTileM), ceil_div(p.n_out, kLayerN));
-  if (backward) DFM_CUDA_CHECK(launch_pdl(mlp_layer_kernel<true>, grid, dim3(kLayerThreads), mlp_layer_smem(), stream, tmA, tmB, p));
-  else          DFM_CUDA_CHECK(launch_pdl(mlp_layer_kernel<false>, grid, dim3(kLayerThreads), mlp_layer_smem(), stream, tmA, tmB, p));
+  if (backward) DFM_CUDA_CHECK(launch_pdl(kPdlBwd, mlp_layer_kernel<true>, grid, dim3(kLayerThreads), mlp_layer_smem(), stream, tmA, tmB, p));
+  else          DFM_CUDA_CHECK(launch_pdl(kPdlFwd, mlp_layer_kernel<false>, grid, dim3(kLayerThreads), mlp_layer_smem(), stream, tmA, tmB, p));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }
 
 int launch_loss_init(const LossParams& p, int rows_pad, cudaStream_t stream) {
-  DFM_CUDA_CHECK(launch_pdl(loss_init_kernel, dim3(ceil_div(rows_pad, 64)), dim3(256), 0, stream, p));
+  DFM_CUDA_CHECK(launch_pdl(kPdlLoss, loss_init_kernel, dim3(ceil_div(rows_pad, 64)), dim3(256), 0, stream, p));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

@@ -29,7 +29,8 @@ __global__ void __launch_bounds__(256)
 dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restrict__ s1,
                  const float* __restrict__ part, int ksplit, size_t part_stride,
                  __nv_bfloat16* __restrict__ Wb, int n,
-                 const StepState* __restrict__ st, const OptHyper hyper, float grad_scale) {
+                 const StepState* __restrict__ st, const OptHyper hyper, float grad_scale, int wb_skip_lo,
+                 int wb_skip_hi) {
   pdl_wait();
   const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
   kstamp(st, kStampDenseOpt);
@@ -40,7 +41,8 @@ dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restric
     float p = P[i], a = s0[i], b = s1[i];
     opt_apply(c, g, p, a, b);
     P[i] = p; s0[i] = a; s1[i] = b;
-    Wb[i] = __float2bfloat16(p);
+    // [wb_skip_lo, wb_skip_hi) = W_0, whose bf16 copy embed_bwd may still be reading: embed_fm_fwd refreshes it
+    if (i < wb_skip_lo || i >= wb_skip_hi) Wb[i] = __float2bfloat16(p);
     if (i == n - 2) {   // fm_bias shares b_out's gradient
       float p2 = P[n - 1], a2 = s0[n - 1], b2 = s1[n - 1];
       opt_apply(c, g, p2, a2, b2);
@@ -58,6 +60,7 @@ __global__ void cast_weights_kernel(const float* __restrict__ P, __nv_bfloat16* 
 
 __global__ void __launch_bounds__(256)
 sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
+  pdl_wait();                       // launched behind embed_bwd with programmatic serialization
   const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
   const int n = a.st->n_unique;
   kstamp(a.st, kStampSparse);
@@ -192,10 +195,10 @@ int launch_set_state(StepState* st, int count, float lr, int train, int step, cu
 
 int launch_dense_opt(float* P, float* s0, float* s1, const float* part, int ksplit, size_t part_stride,
                      __nv_bfloat16* Wb, int n, const StepState* st, const OptHyper& h, float grad_scale,
-                     cudaStream_t stream) {
+                     int wb_skip_lo, int wb_skip_hi, cudaStream_t stream) {
   const int grid = std::min(148 * 8, ceil_div(n, 256));
-  DFM_CUDA_CHECK(launch_pdl(dense_opt_kernel, dim3(grid), dim3(256), 0, stream, P, s0, s1, part, ksplit, part_stride, Wb, n, st, h,
-                            grad_scale));
+  DFM_CUDA_CHECK(launch_pdl(kPdlDense, dense_opt_kernel, dim3(grid), dim3(256), 0, stream, P, s0, s1, part, ksplit, part_stride, Wb,
+                            n, st, h, grad_scale, wb_skip_lo, wb_skip_hi));
   return DFM_OK;
 }
 
@@ -212,7 +215,7 @@ int launch_sparse_apply(const SparseArgs& a, const OptHyper& h, int max_rows, bo
     table_dense_kernel<<<grid, 256, 0, stream>>>(a, h);
   } else {
     const int grid = std::max(1, std::min(148 * 8, ceil_div(max_rows, 16)));
-    sparse_apply_kernel<<<grid, 256, 0, stream>>>(a, h);
+    DFM_CUDA_CHECK(launch_pdl(kPdlSparse, sparse_apply_kernel, dim3(grid), dim3(256), 0, stream, a, h));
   }
   DFM_LAUNCH_CHECK();
   return DFM_OK;

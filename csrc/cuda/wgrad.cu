@@ -143,7 +143,9 @@ int wgrad_set_smem() {
 }
 
 int launch_wgrad(const WgradMaps& maps, const WgradParams& prm, int n_items, cudaStream_t stream) {
-  DFM_CUDA_CHECK(launch_pdl(wgrad_kernel, dim3(n_items), dim3(kWgThreads), wgrad_smem(), stream, maps, prm));
+  // plain launch: on its stream it follows a cross-stream event wait (not a kernel), so there is nothing to overlap
+  wgrad_kernel<<<n_items, kWgThreads, wgrad_smem(), stream>>>(maps, prm);
+  DFM_LAUNCH_CHECK();
   return DFM_OK;
 }
 
