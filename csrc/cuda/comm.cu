@@ -152,26 +152,49 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   }
   // ---------------- phase 0b: push my sparse records to every rank ----------------
   // wire record = wp words: [hw words of bf16 pairs | first-order gradient fp32 | id]; bf16 on the wire halves
-  // the all-gather's NVLink bytes (the accumulation on the receiving side is fp32, in rank order)
-  for (int s = warp_g; s < n_mine; s += warps) {
-    const int id = a.uniq_ids[s];
-    float* grow = a.G + size_t(s) * gp;
-    for (int w = lane; w < hw + 2; w += 32) {
-      uint32_t word;
-      if (w < hw) {
-        const float2 x = *reinterpret_cast<const float2*>(grow + 2 * w);
-        *reinterpret_cast<float2*>(grow + 2 * w) = make_float2(0.f, 0.f);
-        word = pack_bf16x2(x.x, x.y);
-      } else if (w == hw) {
-        word = __float_as_uint(grow[Ke]);
-        grow[Ke] = 0.f;
-      } else {
-        word = uint32_t(id);
+  // the all-gather's NVLink bytes (the accumulation on the receiving side is fp32, in rank order).
+  // LPR = Ke/4 lanes serve one record (four columns each), so a warp moves G = 32/LPR records per instruction and
+  // keeps kRows * G of them in flight.  Record s belongs to group s / G; group gi is handled by warp gi % warps
+  // on EVERY rank and in every phase -- so the per-CTA barrier below covers exactly what a CTA reads afterwards.
+  constexpr int kRows = 2;
+  const int LPR = Ke >> 2, G = 32 / LPR;
+  const int g = lane / LPR, sub = lane - g * LPR;
+  const bool lane_on = g < G;
+  {
+    const int n_groups = (n_mine + G - 1) / G;
+    for (int gi0 = warp_g; gi0 < n_groups; gi0 += warps * kRows) {
+      int sidx[kRows], id[kRows];
+      float4 x[kRows];
+      float gw[kRows];
+#pragma unroll
+      for (int j = 0; j < kRows; ++j) {
+        sidx[j] = (gi0 + j * warps) * G + g;
+        const bool on = lane_on && sidx[j] < n_mine;
+        id[j] = on ? a.uniq_ids[sidx[j]] : -1;
+        x[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        gw[j] = 0.f;
+        if (on) {
+          const float* grow = a.G + size_t(sidx[j]) * gp;
+          x[j] = *reinterpret_cast<const float4*>(grow + 4 * sub);
+          if (sub == 0) gw[j] = grow[Ke];
+        }
       }
-      for (int r = 0; r < N; ++r)
-        (reinterpret_cast<uint32_t*>(cv.base[r] + cv.off_in_rows) + (size_t(cv.rank) * cv.cap + s) * wp)[w] = word;
+#pragma unroll
+      for (int j = 0; j < kRows; ++j) {
+        if (id[j] < 0) continue;
+        float* grow = a.G + size_t(sidx[j]) * gp;
+        *reinterpret_cast<float4*>(grow + 4 * sub) = make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint2 w2 = make_uint2(pack_bf16x2(x[j].x, x[j].y), pack_bf16x2(x[j].z, x[j].w));
+        const uint2 tail = make_uint2(__float_as_uint(gw[j]), uint32_t(id[j]));
+        const size_t off = (size_t(cv.rank) * cv.cap + sidx[j]) * wp;
+        for (int r = 0; r < N; ++r) {
+          uint32_t* dst = reinterpret_cast<uint32_t*>(cv.base[r] + cv.off_in_rows) + off;
+          *reinterpret_cast<uint2*>(dst + 2 * sub) = w2;
+          if (sub == 0) *reinterpret_cast<uint2*>(dst + hw) = tail;
+        }
+        if (sub == 0) { grow[Ke] = 0.f; a.slot_of[id[j]] = -1; }
+      }
     }
-    if (lane == 0) a.slot_of[id] = -1;
   }
   if (threadIdx.x < N)
     reinterpret_cast<int*>(cv.base[threadIdx.x] + cv.off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n_mine;
@@ -206,20 +229,19 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   stamp(cv, 3);
 
   // ---------------- phase 1b: index the records I received by (id, sender) ----------------
-  // The records pushed by CTA b of rank r are those with row s = b*wpc + w + j*warps (w < wpc): exactly the
-  // rows this CTA's barrier covered.  One thread per record; entries carry the epoch, so stale ones are ignored.
+  // CTA b reads the groups its namesakes on the other ranks pushed (gi % warps in [b*wpc, (b+1)*wpc)).  One thread
+  // per (sender, warp slot, record of the group); entries carry the epoch, so stale ones are ignored.
   const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_count);
   const uint32_t* in_rows = reinterpret_cast<const uint32_t*>(cv.base[cv.rank] + cv.off_in_rows);
   const int first_warp = blockIdx.x * wpc;
-  for (int r = 0; r < N; ++r) {
+  for (int t = threadIdx.x; t < N * wpc * G; t += blockDim.x) {
+    const int r = t / (wpc * G), u = t - r * (wpc * G);
+    const int wi = u / G, gg = u - wi * G;
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
-    const int per_cta = nr > first_warp ? ((nr - first_warp + warps - 1) / warps) * wpc : 0;
-    for (int t = threadIdx.x; t < per_cta; t += blockDim.x) {
-      const int s = first_warp + (t % wpc) + (t / wpc) * warps;
-      if (s < nr) {
-        const int id = int(__ldcg(in_rows + (size_t(r) * cv.cap + s) * wp + hw + 1));
-        entry_of[size_t(id) * N + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(s + 1);
-      }
+    for (int gi = first_warp + wi; gi * G + gg < nr; gi += warps) {
+      const int sr = gi * G + gg;
+      const int id = int(__ldcg(in_rows + (size_t(r) * cv.cap + sr) * wp + hw + 1));
+      entry_of[size_t(id) * N + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(sr + 1);
     }
   }
   stamp(cv, 4);
@@ -227,76 +249,76 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   stamp(cv, 5);
 
   // ---------------- phase 2: owners merge and apply ----------------
-  // One warp per received record, kRows records in flight per warp (each is a chain of dependent loads:
-  // id -> {index row, table row} -> senders' records).  Lane l owns columns 2l, 2l+1; lane 0 also owns fm_w.
-  constexpr int kRows = 2;
-  const bool col_lane = lane < hw;
-  for (int r = 0; r < N; ++r) {
-    const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
-    for (int s0 = warp_g; s0 < nr; s0 += warps * kRows) {
-      int id[kRows], sidx[kRows];
-      bool own[kRows];
+  // Work items of a warp: (sender r, round k) -> group k*warps + warp_g of sender r; kRows items in flight.  Each
+  // record is a chain id -> {index row, table row (speculative: needed if this record owns the id)} -> the
+  // senders' records.  The lowest-ranked sender of an id owns it; it sums all senders in rank order.
+  int nr_l = lane < N ? ld_volatile_i(in_count + lane * kCommMaxCtas + blockIdx.x) : 0;
+  int nr_max = nr_l;
 #pragma unroll
-      for (int j = 0; j < kRows; ++j) {
-        const int s = s0 + j * warps;
-        id[j] = s < nr ? int(__ldcg(in_rows + (size_t(r) * cv.cap + s) * wp + hw + 1)) : -1;
+  for (int o = 16; o > 0; o >>= 1) nr_max = max(nr_max, __shfl_xor_sync(0xffffffffu, nr_max, o));
+  const int k_rounds = ((nr_max + G - 1) / G + warps - 1) / warps;
+  const int n_items = k_rounds * N;
+  const unsigned grp_mask = LPR >= 32 ? 0xffffffffu : ((1u << LPR) - 1u);
+  for (int it0 = 0; it0 < n_items; it0 += kRows) {
+    int id[kRows], rr[kRows], ent[kRows];
+    float4 p[kRows], m[kRows], v[kRows];
+    float pw[kRows], mw[kRows], vw[kRows];
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      const int it = it0 + j;
+      const int k = it / N;
+      rr[j] = it - k * N;
+      const int nr = __shfl_sync(0xffffffffu, nr_l, rr[j] & 31);
+      const int sr = (k * warps + warp_g) * G + g;
+      const bool on = lane_on && it < n_items && sr < nr;
+      id[j] = on ? int(__ldcg(in_rows + (size_t(rr[j]) * cv.cap + sr) * wp + hw + 1)) : -1;
+    }
+#pragma unroll
+    for (int j = 0; j < kRows; ++j) {
+      ent[j] = 0;
+      if (id[j] >= 0) {
+        // lane sub reads the entry of sender sub (and sub + LPR when there are more ranks than lanes per record)
+        if (sub < N) {
+          const unsigned long long e = __ldcg(entry_of + size_t(id[j]) * N + sub);
+          if (unsigned(e >> 32) == epoch) ent[j] = int(unsigned(e));
+        }
+        const size_t pi = size_t(id[j]) * Ke + 4 * sub;
+        p[j] = *reinterpret_cast<const float4*>(a.fm_v + pi);
+        m[j] = *reinterpret_cast<const float4*>(a.v_s0 + pi);
+        v[j] = *reinterpret_cast<const float4*>(a.v_s1 + pi);
+        if (sub == 0) { pw[j] = a.fm_w[id[j]]; mw[j] = a.w_s0[id[j]]; vw[j] = a.w_s1[id[j]]; }
       }
-      // index row and (speculatively, it is needed if this record turns out to own the id) the table row
-      float2 p[kRows], m[kRows], v[kRows];
-      float pw[kRows], mw[kRows], vw[kRows];
+    }
 #pragma unroll
-      for (int j = 0; j < kRows; ++j) {
-        sidx[j] = 0;
-        if (id[j] >= 0) {
-          if (lane < N) {
-            const unsigned long long e = __ldcg(entry_of + size_t(id[j]) * N + lane);
-            if (unsigned(e >> 32) == epoch) sidx[j] = int(unsigned(e));
-          }
-          if (col_lane) {
-            const size_t pi = size_t(id[j]) * Ke + 2 * lane;
-            p[j] = *reinterpret_cast<const float2*>(a.fm_v + pi);
-            m[j] = *reinterpret_cast<const float2*>(a.v_s0 + pi);
-            v[j] = *reinterpret_cast<const float2*>(a.v_s1 + pi);
-          }
-          if (lane == 0) { pw[j] = a.fm_w[id[j]]; mw[j] = a.w_s0[id[j]]; vw[j] = a.w_s1[id[j]]; }
+    for (int j = 0; j < kRows; ++j) {
+      const unsigned have = (__ballot_sync(0xffffffffu, ent[j] != 0) >> (lane_on ? g * LPR : 0)) & grp_mask;
+      const bool own = id[j] >= 0 && (__ffs(have) - 1) == rr[j];
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      float accw = 0.f;
+#pragma unroll
+      for (int q = 0; q < kCommMaxRanks; ++q) {             // rank order: identical sum on every replica
+        const int e = __shfl_sync(0xffffffffu, ent[j], lane_on ? g * LPR + (q < LPR ? q : 0) : lane);
+        if (own && q < N && e) {
+          const uint32_t* row = in_rows + (size_t(q) * cv.cap + (e - 1)) * wp;
+          const uint2 w2 = __ldcg(reinterpret_cast<const uint2*>(row + 2 * sub));
+          const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&w2.x);
+          const __nv_bfloat162 b1 = *reinterpret_cast<const __nv_bfloat162*>(&w2.y);
+          acc.x += __low2float(b0); acc.y += __high2float(b0);
+          acc.z += __low2float(b1); acc.w += __high2float(b1);
+          if (sub == 0) accw += __uint_as_float(__ldcg(row + hw));
         }
       }
-      float2 acc[kRows];
-      float accw[kRows];
-#pragma unroll
-      for (int j = 0; j < kRows; ++j) {
-        const unsigned mask = __ballot_sync(0xffffffffu, sidx[j] != 0);
-        own[j] = id[j] >= 0 && (__ffs(mask) - 1) == r;     // the lowest-ranked sender of this id applies it
-        acc[j] = make_float2(0.f, 0.f);
-        accw[j] = 0.f;
-#pragma unroll
-        for (int q = 0; q < kCommMaxRanks; ++q) {           // rank order: identical sum on every replica
-          const int e = __shfl_sync(0xffffffffu, sidx[j], q);
-          if (own[j] && e) {
-            const uint32_t* row = in_rows + (size_t(q) * cv.cap + (e - 1)) * wp;
-            if (col_lane) {
-              const uint32_t w2 = __ldcg(row + lane);
-              const __nv_bfloat162 b2 = *reinterpret_cast<const __nv_bfloat162*>(&w2);
-              acc[j].x += __low2float(b2);
-              acc[j].y += __high2float(b2);
-            }
-            if (lane == 0) accw[j] += __uint_as_float(__ldcg(row + hw));
-          }
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < kRows; ++j) {
-        if (!own[j]) continue;
-        if (col_lane) {
-          const size_t pi = size_t(id[j]) * Ke + 2 * lane;
-          opt_apply(c, acc[j].x * inv_n + hyper.l2_reg * p[j].x, p[j].x, m[j].x, v[j].x);
-          opt_apply(c, acc[j].y * inv_n + hyper.l2_reg * p[j].y, p[j].y, m[j].y, v[j].y);
-          *reinterpret_cast<float2*>(a.fm_v + pi) = p[j];
-          *reinterpret_cast<float2*>(a.v_s0 + pi) = m[j];
-          *reinterpret_cast<float2*>(a.v_s1 + pi) = v[j];
-        }
-        if (lane == 0) {
-          opt_apply(c, accw[j] * inv_n + hyper.l2_reg * pw[j], pw[j], mw[j], vw[j]);
+      if (own) {
+        const size_t pi = size_t(id[j]) * Ke + 4 * sub;
+        opt_apply(c, acc.x * inv_n + hyper.l2_reg * p[j].x, p[j].x, m[j].x, v[j].x);
+        opt_apply(c, acc.y * inv_n + hyper.l2_reg * p[j].y, p[j].y, m[j].y, v[j].y);
+        opt_apply(c, acc.z * inv_n + hyper.l2_reg * p[j].z, p[j].z, m[j].z, v[j].z);
+        opt_apply(c, acc.w * inv_n + hyper.l2_reg * p[j].w, p[j].w, m[j].w, v[j].w);
+        *reinterpret_cast<float4*>(a.fm_v + pi) = p[j];
+        *reinterpret_cast<float4*>(a.v_s0 + pi) = m[j];
+        *reinterpret_cast<float4*>(a.v_s1 + pi) = v[j];
+        if (sub == 0) {
+          opt_apply(c, accw * inv_n + hyper.l2_reg * pw[j], pw[j], mw[j], vw[j]);
           a.fm_w[id[j]] = pw[j]; a.w_s0[id[j]] = mw[j]; a.w_s1[id[j]] = vw[j];
         }
       }

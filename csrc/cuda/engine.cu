@@ -438,6 +438,9 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
               world, rank);
   DFM_REQUIRE(E->cfg.table_update_mode == DFM_TABLE_LAZY, "multi-GPU fused path implements the lazy table update");
   DFM_REQUIRE(!E->symm, "comm already allocated");
+  // the merge phase gives one lane per sender out of the embedding_size/4 lanes that serve a record
+  DFM_REQUIRE(world <= E->cfg.embedding_size / 4, "multi-GPU fused path: world %d needs embedding_size >= %d", world,
+              4 * world);
   CommView& cv = E->cv;
   cv.world = world; cv.rank = rank;
   cv.cap = E->cfg.batch_max * E->cfg.field_size;
