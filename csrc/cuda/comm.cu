@@ -82,17 +82,21 @@ static __device__ __noinline__ void comm_watchdog_trip(int rank, int what, int p
   __trap();
 }
 
-// Barrier among the CTAs with index blockIdx.x of all ranks.  bar.sync orders every thread's earlier
-// writes before the signalling threads, and their release store at system scope is cumulative over
-// those writes: no separate membar.sys is needed (measured: a system fence costs ~4 us here, and
-// st.release.sys contains one).
-__device__ __forceinline__ void cta_barrier_all_ranks(const CommView& cv, unsigned int epoch) {
+// Barrier among the CTAs with index blockIdx.x of all ranks, split into signal and wait.  bar.sync orders every
+// thread's earlier writes before the signalling threads, and their release store at system scope is cumulative
+// over those writes: no separate membar.sys is needed (measured: a system fence costs ~4 us here, and
+// st.release.sys contains one).  `off` selects the flag array (two rounds per step use two arrays).
+__device__ __forceinline__ void cta_signal_all_ranks(const CommView& cv, size_t off, unsigned int epoch) {
   __syncthreads();
+  if (threadIdx.x < cv.world) {
+    unsigned int* peer_flags = reinterpret_cast<unsigned int*>(cv.base[threadIdx.x] + off);
+    st_release_sys(peer_flags + size_t(cv.rank) * kCommMaxCtas + blockIdx.x, epoch);
+  }
+}
+__device__ __forceinline__ void cta_wait_all_ranks(const CommView& cv, size_t off, unsigned int epoch) {
   const int t = threadIdx.x;
   if (t < cv.world) {
-    unsigned int* peer_flags = reinterpret_cast<unsigned int*>(cv.base[t] + cv.off_flags);
-    st_release_sys(peer_flags + size_t(cv.rank) * kCommMaxCtas + blockIdx.x, epoch);
-    const unsigned int* mine = reinterpret_cast<const unsigned int*>(cv.base[cv.rank] + cv.off_flags) +
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(cv.base[cv.rank] + off) +
                                size_t(t) * kCommMaxCtas + blockIdx.x;
     const long long t0 = clock64();
     while (ld_relaxed_sys(mine) < epoch)
@@ -101,12 +105,23 @@ __device__ __forceinline__ void cta_barrier_all_ranks(const CommView& cv, unsign
   }
   __syncthreads();
 }
+__device__ __forceinline__ void cta_barrier_all_ranks(const CommView& cv, unsigned int epoch) {
+  cta_signal_all_ranks(cv, cv.off_flags, epoch);
+  cta_wait_all_ranks(cv, cv.off_flags, epoch);
+}
 
-// Barrier among all CTAs of this GPU's grid (they are co-resident).  `bar` only ever grows.
-__device__ __forceinline__ void grid_barrier(const CommView& cv, unsigned int* bar, unsigned int epoch) {
+__device__ __forceinline__ void st_volatile_f4(float* p, const float4& v) {
+  asm volatile("st.volatile.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Barrier among all CTAs of this GPU's grid (they are co-resident), split into arrive and wait so that work which
+// does not depend on the other CTAs can sit between the two.  `bar` only ever grows.
+__device__ __forceinline__ void grid_arrive(unsigned int* bar) {
   __syncthreads();
+  if (threadIdx.x == 0) red_release_gpu_add(bar, 1u);
+}
+__device__ __forceinline__ void grid_wait(const CommView& cv, unsigned int* bar, unsigned int epoch) {
   if (threadIdx.x == 0) {
-    red_release_gpu_add(bar, 1u);
     const unsigned int target = epoch * gridDim.x;
     const long long t0 = clock64();
     while (ld_acquire_gpu(bar) < target)
@@ -137,18 +152,35 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   const int n4 = (n_red + 3) / 4;
   const int per = (n4 + gridDim.x - 1) / gridDim.x;
   const int g_lo = blockIdx.x * per, g_hi = min(g_lo + per, n4);
-  float* my_dP = reinterpret_cast<float*>(cv.base[cv.rank] + cv.off_dP);
+  const size_t par = epoch & 1u;
+  const size_t off_dP = cv.off_dP + par * cv.dP_bytes;
+  const size_t off_in_count = cv.off_in_count + par * cv.in_count_bytes;
+  const size_t off_in_rows = cv.off_in_rows + par * cv.in_rows_bytes;
+  float* my_dP = reinterpret_cast<float*>(cv.base[cv.rank] + off_dP);
 
   stamp(cv, 0);
   kstamp(a.st, kStampSparse);
   // ---------------- phase 0a: local sum of the split-K slices ----------------
-  for (int g = g_lo + threadIdx.x; g < g_hi; g += blockDim.x) {
+  // A CTA sums exactly the groups its namesakes on the other ranks read after the barrier (the per-CTA flags only
+  // cover what the same-numbered CTA wrote): [g_lo, g_hi) for the one-shot all-reduce, sub-slice b of every
+  // rank's chunk for the two-shot one.
+  const int c4 = (n4 + N - 1) / N;                     // groups per rank chunk
+  const int per2 = (c4 + gridDim.x - 1) / gridDim.x;   // groups per CTA sub-slice
+  auto local_sum = [&](int gq) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int k = 0; k < d.ksplit; ++k) {
-      const float4 v = *reinterpret_cast<const float4*>(d.part + size_t(k) * d.part_stride + 4 * size_t(g));
+      const float4 v = *reinterpret_cast<const float4*>(d.part + size_t(k) * d.part_stride + 4 * size_t(gq));
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
-    *reinterpret_cast<float4*>(my_dP + 4 * size_t(g)) = acc;
+    *reinterpret_cast<float4*>(my_dP + 4 * size_t(gq)) = acc;
+  };
+  if (cv.two_shot) {
+    for (int q = 0; q < N; ++q) {
+      const int lo = q * c4 + blockIdx.x * per2, hi = min(min(lo + per2, (q + 1) * c4), n4);
+      for (int gq = lo + threadIdx.x; gq < hi; gq += blockDim.x) local_sum(gq);
+    }
+  } else {
+    for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += blockDim.x) local_sum(gq);
   }
   // ---------------- phase 0b: push my sparse records to every rank ----------------
   // wire record = wp words: [hw words of bf16 pairs | first-order gradient fp32 | id]; bf16 on the wire halves
@@ -188,7 +220,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
         const uint2 tail = make_uint2(__float_as_uint(gw[j]), uint32_t(id[j]));
         const size_t off = (size_t(cv.rank) * cv.cap + sidx[j]) * wp;
         for (int r = 0; r < N; ++r) {
-          uint32_t* dst = reinterpret_cast<uint32_t*>(cv.base[r] + cv.off_in_rows) + off;
+          uint32_t* dst = reinterpret_cast<uint32_t*>(cv.base[r] + off_in_rows) + off;
           *reinterpret_cast<uint2*>(dst + 2 * sub) = w2;
           if (sub == 0) *reinterpret_cast<uint2*>(dst + hw) = tail;
         }
@@ -197,42 +229,37 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
     }
   }
   if (threadIdx.x < N)
-    reinterpret_cast<int*>(cv.base[threadIdx.x] + cv.off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n_mine;
+    reinterpret_cast<int*>(cv.base[threadIdx.x] + off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n_mine;
   stamp(cv, 1);
   cta_barrier_all_ranks(cv, epoch);
   stamp(cv, 2);
 
-  // ---------------- phase 1a: dense one-shot all-reduce + optimizer on my groups ----------------
-  for (int g = g_lo + threadIdx.x; g < g_hi; g += blockDim.x) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  // ---------------- phase 1a: two-shot dense all-reduce, first half ----------------
+  // Rank r owns chunk r of the gradient vector; CTA b a sub-slice of it: it sums the N copies in rank order
+  // (identical on every replica by construction: only one rank computes each sum) and stores the sum back into
+  // every rank's copy, in place -- nobody else touches that sub-slice.  NVLink moves 2 (N-1)/N of the vector per
+  // rank instead of the one-shot's N-1 copies; the second cross-GPU round is only signalled here and waited for
+  // after the index phase.
+  if (cv.two_shot) {
+    const int lo = cv.rank * c4 + blockIdx.x * per2, hi = min(min(lo + per2, (cv.rank + 1) * c4), n4);
+    for (int gq = lo + threadIdx.x; gq < hi; gq += blockDim.x) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 4
-    for (int q = 0; q < N; ++q) {                      // rank order: identical sum on every replica
-      const float4 v = ld_volatile_f4(reinterpret_cast<const float*>(cv.base[q] + cv.off_dP) + 4 * size_t(g));
-      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-    }
-    const float gr[4] = {acc.x * inv_n, acc.y * inv_n, acc.z * inv_n, acc.w * inv_n};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int i = 4 * g + j;
-      if (i >= n_red) break;
-      float p = d.P[i], m = d.s0[i], v = d.s1[i];
-      opt_apply(c, gr[j], p, m, v);
-      d.P[i] = p; d.s0[i] = m; d.s1[i] = v;
-      d.Wb[i] = __float2bfloat16(p);
-      if (i == d.n - 2) {                              // fm_bias shares b_out's gradient
-        float p2 = d.P[d.n - 1], m2 = d.s0[d.n - 1], v2 = d.s1[d.n - 1];
-        opt_apply(c, gr[j], p2, m2, v2);
-        d.P[d.n - 1] = p2; d.s0[d.n - 1] = m2; d.s1[d.n - 1] = v2;
+      for (int q = 0; q < N; ++q) {
+        const float4 v = ld_volatile_f4(reinterpret_cast<const float*>(cv.base[q] + off_dP) + 4 * size_t(gq));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
+      for (int q = 0; q < N; ++q)
+        st_volatile_f4(reinterpret_cast<float*>(cv.base[q] + off_dP) + 4 * size_t(gq), acc);
     }
+    cta_signal_all_ranks(cv, cv.off_flags2, epoch);
   }
-  stamp(cv, 3);
 
   // ---------------- phase 1b: index the records I received by (id, sender) ----------------
   // CTA b reads the groups its namesakes on the other ranks pushed (gi % warps in [b*wpc, (b+1)*wpc)).  One thread
   // per (sender, warp slot, record of the group); entries carry the epoch, so stale ones are ignored.
-  const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + cv.off_in_count);
-  const uint32_t* in_rows = reinterpret_cast<const uint32_t*>(cv.base[cv.rank] + cv.off_in_rows);
+  const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + off_in_count);
+  const uint32_t* in_rows = reinterpret_cast<const uint32_t*>(cv.base[cv.rank] + off_in_rows);
   const int first_warp = blockIdx.x * wpc;
   for (int t = threadIdx.x; t < N * wpc * G; t += blockDim.x) {
     const int r = t / (wpc * G), u = t - r * (wpc * G);
@@ -244,8 +271,50 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       entry_of[size_t(id) * N + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(sr + 1);
     }
   }
+  stamp(cv, 3);
+  grid_arrive(grid_bar);
+
+  // ---------------- phase 1c: dense optimizer on the averaged gradient ----------------
+  auto apply_group = [&](int gq, const float4& sum) {
+    const float gr[4] = {sum.x * inv_n, sum.y * inv_n, sum.z * inv_n, sum.w * inv_n};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int i = 4 * gq + j;
+      if (i >= n_red) break;
+      float p = d.P[i], m = d.s0[i], v = d.s1[i];
+      opt_apply(c, gr[j], p, m, v);
+      d.P[i] = p; d.s0[i] = m; d.s1[i] = v;
+      d.Wb[i] = __float2bfloat16(p);
+      if (i == d.n - 2) {                              // fm_bias shares b_out's gradient
+        float p2 = d.P[d.n - 1], m2 = d.s0[d.n - 1], v2 = d.s1[d.n - 1];
+        opt_apply(c, gr[j], p2, m2, v2);
+        d.P[d.n - 1] = p2; d.s0[d.n - 1] = m2; d.s1[d.n - 1] = v2;
+      }
+    }
+  };
+  if (cv.two_shot) {
+    // the sums of my namesake CTAs' sub-slices (one per rank's chunk) have landed in my dP once their flags are up
+    cta_wait_all_ranks(cv, cv.off_flags2, epoch);
+    for (int q = 0; q < N; ++q) {
+      const int lo = q * c4 + blockIdx.x * per2, hi = min(min(lo + per2, (q + 1) * c4), n4);
+      for (int gq = lo + threadIdx.x; gq < hi; gq += blockDim.x)
+        apply_group(gq, ld_volatile_f4(my_dP + 4 * size_t(gq)));
+    }
+  } else {
+    // one-shot all-reduce: every rank reads all N copies of its groups
+    for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += blockDim.x) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+      for (int q = 0; q < N; ++q) {                    // rank order: identical sum on every replica
+        const float4 v = ld_volatile_f4(reinterpret_cast<const float*>(cv.base[q] + off_dP) + 4 * size_t(gq));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      apply_group(gq, acc);
+    }
+  }
+  // (sits between the grid barrier's arrive and wait: it hides the barrier and the index phase's imbalance)
   stamp(cv, 4);
-  grid_barrier(cv, grid_bar, epoch);
+  grid_wait(cv, grid_bar, epoch);
   stamp(cv, 5);
 
   // ---------------- phase 2: owners merge and apply ----------------

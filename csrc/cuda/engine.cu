@@ -449,10 +449,18 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
   size_t o = 0;
   const size_t n4 = size_t(round_up(E->n_dense, 4)) + 8;
-  cv.off_dP = o;        o = align(o + n4 * 4);
+  cv.dP_bytes = align(n4 * 4);
+  cv.in_count_bytes = align(size_t(world) * kCommMaxCtas * 4);
+  cv.in_rows_bytes = align(size_t(world) * cv.cap * cv.row_pitch * 4);
+  cv.off_dP = o;        o += 2 * cv.dP_bytes;
   cv.off_flags = o;     o = align(o + size_t(world) * kCommMaxCtas * 4);
-  cv.off_in_count = o;  o = align(o + size_t(world) * kCommMaxCtas * 4);
-  cv.off_in_rows = o;   o = align(o + size_t(world) * cv.cap * cv.row_pitch * 4);
+  cv.off_flags2 = o;    o = align(o + size_t(world) * kCommMaxCtas * 4);
+  cv.off_in_count = o;  o += 2 * cv.in_count_bytes;
+  cv.off_in_rows = o;   o += 2 * cv.in_rows_bytes;
+  {
+    const char* v = getenv("DFM_DENSE_TWO_SHOT");
+    cv.two_shot = v ? atoi(v) : (world > 2);
+  }
   E->symm_bytes = o;
   void* p = nullptr;
   DFM_CUDA_CHECK(cudaMalloc(&p, o));

@@ -242,7 +242,12 @@ struct CommView {
   int cap;            // inbox rows per sender (= batch_max * field_size)
   int row_pitch;      // 32-bit words per inbox record: Ke/2 bf16 pairs, first-order gradient (fp32), id; whole sectors
   int ctas;           // grid of the exchange kernel: <= one CTA per SM, all co-resident
-  size_t off_dP, off_flags, off_in_count, off_in_rows;
+  size_t off_dP, off_flags, off_flags2, off_in_count, off_in_rows;
+  // dP, in_count and in_rows exist twice and alternate with the step parity: a rank that is already pushing step
+  // k+1 never writes what a slower peer may still be reading for step k (it cannot get two steps ahead: it needs
+  // that peer's step-k+1 flag first)
+  size_t dP_bytes, in_count_bytes, in_rows_bytes;
+  int two_shot;       // dense all-reduce as reduce-scatter + all-gather (world > 2) instead of one-shot
   unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
 };
 

@@ -90,8 +90,8 @@ for _ in range(100):
 e1.record(); torch.cuda.synchronize()
 res["fused_us_per_step_B512"] = round(e0.elapsed_time(e1) * 10, 2)
 dbg = fused.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)
-names = {0: "start", 1: "local_sum+push_done", 2: "barrier_done", 3: "dense_apply_done", 4: "index_done",
-         5: "grid_barrier_done", 6: "merge_apply_done"}
+names = {0: "start", 1: "local_sum+push_done", 2: "barrier_done", 3: "index_done", 4: "dense_apply_done",
+         5: "grid_wait_done", 6: "merge_apply_done"}
 t0 = int(dbg[0])
 res["comm_phases_us"] = {names[i]: round((int(dbg[i]) - t0) / 1000.0, 2) for i in sorted(names)}
 # Adam turns tiny bf16 differences of near-zero gradients into full-size steps; GD is the sharp check
