@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(kXThreads, 1)
 exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, const DenseArgs d,
                       unsigned long long* __restrict__ entry_of, unsigned int* __restrict__ grid_bar,
                       const OptHyper hyper) {
-  const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
+  const OptStepConsts c = make_opt_consts(hyper, a.st);
   const unsigned int epoch = unsigned(a.st->comm_epoch);       // bumped by the first kernel of the step
   const int N = cv.world, Ke = a.Ke;
   const int wp = cv.row_pitch;                         // 32-bit words per wire record

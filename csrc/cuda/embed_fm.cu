@@ -48,6 +48,7 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
     if (dedupe) {                  // == training step: open optimizer step (see StepState::step)
       st->step += 1;
       st->comm_epoch += 1;
+      open_step_consts(st);
       st->n_unique = 0;            // counted by dedupe, which is queued behind this kernel
       st->n_union = 0;             // counted by the multi-GPU claim pass
     }
@@ -157,6 +158,7 @@ embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ va
     if (dedupe) {
       st->step += 1;
       st->comm_epoch += 1;
+      open_step_consts(st);
       st->n_unique = 0;
       st->n_union = 0;
     }

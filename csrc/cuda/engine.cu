@@ -204,6 +204,7 @@ static int engine_build(Engine& E) {
 
   StepState init{};
   init.count = c.batch_max; init.step = 0; init.lr = c.lr; init.train = 1;
+  if (E.hyper.kind == DFM_OPT_ADAM) { init.adam_b1 = E.hyper.beta1; init.adam_b2 = E.hyper.beta2; init.lr_t = c.lr; }
   DFM_CUDA_CHECK(cudaMemcpy(E.st, &init, sizeof(init), cudaMemcpyHostToDevice));
   if ((rc = launch_cast_weights(E.t.dense, E.Wb, E.n_dense, nullptr))) return rc;
   DFM_CUDA_CHECK(cudaDeviceSynchronize());
@@ -459,7 +460,7 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   cv.off_in_rows = o;   o += 2 * cv.in_rows_bytes;
   {
     const char* v = getenv("DFM_DENSE_TWO_SHOT");
-    cv.two_shot = v ? atoi(v) : (world > 2);
+    cv.two_shot = v ? atoi(v) : 0;   // measured on 2, 4 and 8 B200s: the one-shot form is 6-8 us faster per step
   }
   E->symm_bytes = o;
   void* p = nullptr;

@@ -31,7 +31,9 @@ struct StepState {
   int train;          // 1: dropout active, gradients produced
   int n_union;        // multi-GPU: distinct rows touched by any rank this step
   int comm_epoch;     // multi-GPU: completed collective rounds (flag value of the next round = +1)
-  int pad[3];
+  float adam_b1, adam_b2;   // > 0 when the optimizer is Adam: the step's first kernel derives lr_t from them
+  float lr_t;               // Adam: lr * sqrt(1 - b2^t) / (1 - b1^t) of the update in flight (one powf pair per step,
+                            // not one per warp of every optimizer kernel)
   // %globaltimer when CTA 0 of each kernel of the last step started (slots: kStamp*); read by the
   // timeline probe (scripts/gpu_timeline.py) to see launch gaps inside the replayed graph
   unsigned long long kstamp[24];
@@ -91,16 +93,20 @@ struct OptStepConsts {
   int kind;
 };
 
-__device__ __forceinline__ OptStepConsts make_opt_consts(const OptHyper& h, float lr, int step) {
+__device__ __forceinline__ OptStepConsts make_opt_consts(const OptHyper& h, const StepState* st) {
   OptStepConsts c;
-  c.kind = h.kind; c.lr = lr; c.b1 = h.beta1; c.b2 = h.beta2; c.eps = h.eps; c.mom = h.momentum;
+  c.kind = h.kind; c.lr = st->lr; c.b1 = h.beta1; c.b2 = h.beta2; c.eps = h.eps; c.mom = h.momentum;
   c.lr_power = h.ftrl_lr_power; c.l1 = h.ftrl_l1; c.l2 = h.ftrl_l2;
-  c.lr_t = lr;
-  if (h.kind == DFM_OPT_ADAM) {
-    const float t = static_cast<float>(step);
-    c.lr_t = lr * sqrtf(1.f - powf(h.beta2, t)) / (1.f - powf(h.beta1, t));
-  }
+  c.lr_t = h.kind == DFM_OPT_ADAM ? st->lr_t : st->lr;
   return c;
+}
+
+// Called by the one thread that opens a training step (after it bumped st->step).
+__device__ __forceinline__ void open_step_consts(StepState* st) {
+  if (st->adam_b1 > 0.f) {
+    const float t = static_cast<float>(st->step);
+    st->lr_t = st->lr * sqrtf(1.f - powf(st->adam_b2, t)) / (1.f - powf(st->adam_b1, t));
+  }
 }
 
 __device__ __forceinline__ void opt_apply(const OptStepConsts& c, float g, float& p, float& s0, float& s1) {
@@ -247,7 +253,7 @@ struct CommView {
   // k+1 never writes what a slower peer may still be reading for step k (it cannot get two steps ahead: it needs
   // that peer's step-k+1 flag first)
   size_t dP_bytes, in_count_bytes, in_rows_bytes;
-  int two_shot;       // dense all-reduce as reduce-scatter + all-gather (world > 2) instead of one-shot
+  int two_shot;       // dense all-reduce as reduce-scatter + all-gather instead of one-shot (DFM_DENSE_TWO_SHOT=1)
   unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
 };
 

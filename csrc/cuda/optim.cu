@@ -32,7 +32,7 @@ dense_opt_kernel(float* __restrict__ P, float* __restrict__ s0, float* __restric
                  const StepState* __restrict__ st, const OptHyper hyper, float grad_scale, int wb_skip_lo,
                  int wb_skip_hi) {
   pdl_wait();
-  const OptStepConsts c = make_opt_consts(hyper, st->lr, st->step);
+  const OptStepConsts c = make_opt_consts(hyper, st);
   kstamp(st, kStampDenseOpt);
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n - 1; i += gridDim.x * blockDim.x) {
     float g = 0.f;
@@ -58,62 +58,45 @@ __global__ void cast_weights_kernel(const float* __restrict__ P, __nv_bfloat16* 
 }
 
 
-__global__ void __launch_bounds__(256)
+// Ke/4 lanes per touched row (four columns each, float4 accesses), so a warp covers 32/(Ke/4) rows per instruction
+// and, at <= 51 registers, an SM keeps 160 rows in flight -- the warp-per-row version it replaces needed 76 registers
+// for two rows per warp (54 rows per SM, 2.7 waves of CTAs for one Criteo batch).  A row is a dependent chain
+// (id -> table row), so what counts is how many chains are in flight.
+__global__ void __launch_bounds__(256, 5)
 sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
   pdl_wait();                       // launched behind embed_bwd with programmatic serialization
-  const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
+  const OptStepConsts c = make_opt_consts(hyper, a.st);
   const int n = a.st->n_unique;
   kstamp(a.st, kStampSparse);
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const int Ke = a.Ke, GP = g_pitch(a.Ke);
-  // One warp per touched row; a row is a chain of dependent loads (id -> table row), so each warp keeps
-  // kRows rows in flight: every stage is issued for all of them before any result is used.
-  constexpr int kRows = 2;
-  constexpr int kKPL = 2;                               // embedding components per lane (Ke <= 64)
-  for (int s0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kRows; s0 < n; s0 += warps * kRows) {
-    int id[kRows];
-    bool live[kRows];
-#pragma unroll
-    for (int j = 0; j < kRows; ++j) {
-      live[j] = s0 + j < n;
-      id[j] = live[j] ? a.uniq_ids[s0 + j] : 0;
-    }
-    // lane l owns columns l, l+32 of the factor row and, for l == 0, the first-order weight (column Ke of G)
-    float g[kRows][kKPL + 1], p[kRows][kKPL + 1], m[kRows][kKPL + 1], v[kRows][kKPL + 1];
-#pragma unroll
-    for (int j = 0; j < kRows; ++j) {
-      if (!live[j]) continue;
-      float* grow = a.G + size_t(s0 + j) * GP;
-#pragma unroll
-      for (int q = 0; q < kKPL; ++q)
-        if (lane + 32 * q < Ke) {
-          const size_t pi = size_t(id[j]) * Ke + lane + 32 * q;
-          g[j][q] = grow[lane + 32 * q];
-          p[j][q] = a.fm_v[pi]; m[j][q] = a.v_s0[pi]; v[j][q] = a.v_s1[pi];
-        }
-      if (lane == 0) {
-        g[j][kKPL] = grow[Ke];
-        p[j][kKPL] = a.fm_w[id[j]]; m[j][kKPL] = a.w_s0[id[j]]; v[j][kKPL] = a.w_s1[id[j]];
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < kRows; ++j) {
-      if (!live[j]) continue;
-      float* grow = a.G + size_t(s0 + j) * GP;
-#pragma unroll
-      for (int q = 0; q < kKPL; ++q)
-        if (lane + 32 * q < Ke) {
-          const size_t pi = size_t(id[j]) * Ke + lane + 32 * q;
-          grow[lane + 32 * q] = 0.f;
-          opt_apply(c, g[j][q] * a.grad_scale + hyper.l2_reg * p[j][q], p[j][q], m[j][q], v[j][q]);
-          a.fm_v[pi] = p[j][q]; a.v_s0[pi] = m[j][q]; a.v_s1[pi] = v[j][q];
-        }
-      if (lane == 0) {
+  const int LPR = Ke >> 2, G = 32 / LPR;
+  const int g = lane / LPR, sub = lane - g * LPR;
+  if (g < G) {
+    for (int s = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * G + g; s < n; s += warps * G) {
+      const int id = a.uniq_ids[s];
+      float* grow = a.G + size_t(s) * GP;
+      const size_t pi = size_t(id) * Ke + 4 * sub;
+      const float4 gr = *reinterpret_cast<const float4*>(grow + 4 * sub);
+      float4 p = *reinterpret_cast<const float4*>(a.fm_v + pi);
+      float4 m = *reinterpret_cast<const float4*>(a.v_s0 + pi);
+      float4 v = *reinterpret_cast<const float4*>(a.v_s1 + pi);
+      float gw = 0.f, pw = 0.f, mw = 0.f, vw = 0.f;
+      if (sub == 0) { gw = grow[Ke]; pw = a.fm_w[id]; mw = a.w_s0[id]; vw = a.w_s1[id]; }
+      *reinterpret_cast<float4*>(grow + 4 * sub) = make_float4(0.f, 0.f, 0.f, 0.f);
+      opt_apply(c, gr.x * a.grad_scale + hyper.l2_reg * p.x, p.x, m.x, v.x);
+      opt_apply(c, gr.y * a.grad_scale + hyper.l2_reg * p.y, p.y, m.y, v.y);
+      opt_apply(c, gr.z * a.grad_scale + hyper.l2_reg * p.z, p.z, m.z, v.z);
+      opt_apply(c, gr.w * a.grad_scale + hyper.l2_reg * p.w, p.w, m.w, v.w);
+      *reinterpret_cast<float4*>(a.fm_v + pi) = p;
+      *reinterpret_cast<float4*>(a.v_s0 + pi) = m;
+      *reinterpret_cast<float4*>(a.v_s1 + pi) = v;
+      if (sub == 0) {
         grow[Ke] = 0.f;
-        opt_apply(c, g[j][kKPL] * a.grad_scale + hyper.l2_reg * p[j][kKPL], p[j][kKPL], m[j][kKPL], v[j][kKPL]);
-        a.fm_w[id[j]] = p[j][kKPL]; a.w_s0[id[j]] = m[j][kKPL]; a.w_s1[id[j]] = v[j][kKPL];
-        a.slot_of[id[j]] = -1;
+        opt_apply(c, gw * a.grad_scale + hyper.l2_reg * pw, pw, mw, vw);
+        a.fm_w[id] = pw; a.w_s0[id] = mw; a.w_s1[id] = vw;
+        a.slot_of[id] = -1;
       }
     }
   }
@@ -123,7 +106,7 @@ sparse_apply_kernel(const SparseArgs a, const OptHyper hyper) {
 // dense_exact: one warp per table row, all rows.
 __global__ void __launch_bounds__(256)
 table_dense_kernel(const SparseArgs a, const OptHyper hyper) {
-  const OptStepConsts c = make_opt_consts(hyper, a.st->lr, a.st->step);
+  const OptStepConsts c = make_opt_consts(hyper, a.st);
   const int lane = threadIdx.x & 31;
   const long long warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
   for (long long id = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; id < a.V; id += warps) {
@@ -214,7 +197,8 @@ int launch_sparse_apply(const SparseArgs& a, const OptHyper& h, int max_rows, bo
     const int grid = int(std::min<long long>(148 * 8, (warps_needed + 7) / 8));
     table_dense_kernel<<<grid, 256, 0, stream>>>(a, h);
   } else {
-    const int grid = std::max(1, std::min(148 * 8, ceil_div(max_rows, 16)));
+    // one CTA covers 8 warps x 32/(Ke/4) rows per pass; 5 CTAs fit an SM
+    const int grid = std::max(1, std::min(148 * 5, ceil_div(max_rows, 8 * (32 / (a.Ke / 4)))));
     DFM_CUDA_CHECK(launch_pdl(kPdlSparse, sparse_apply_kernel, dim3(grid), dim3(256), 0, stream, a, h));
   }
   DFM_LAUNCH_CHECK();
