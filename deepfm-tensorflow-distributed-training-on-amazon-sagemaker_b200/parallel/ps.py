@@ -265,6 +265,8 @@ def _cluster(flags, env) -> Tuple[int, int, str, int]:
         ttype, tidx = task.get("type", "worker"), int(task.get("index", 0))
         if ttype == "ps":
             return n_ps, n_workers, "ps", tidx
+        if ttype == "evaluator":                         # outside the training cluster (set_dist_env mode 2)
+            return n_ps, n_workers, "evaluator", tidx
         has_chief = bool(cl.get("master") or cl.get("chief"))
         return n_ps, n_workers, "worker", tidx + (1 if ttype == "worker" and has_chief else 0)
     n_ps = len([h for h in str(flags.ps_hosts).split(",") if h]) or int(os.environ.get("DFM_NUM_PS", "1"))
@@ -288,6 +290,9 @@ def run_ps(flags, env) -> int:
     from ..utils.metrics import StreamingAUC
 
     n_ps, n_workers, role, index = _cluster(flags, env)
+    if role == "evaluator":
+        print("[ps] evaluator task: evaluation is run by the chief on its throttle (PS.py:501-521); nothing to do")
+        return 0
     rank = index if role == "ps" else n_ps + index
     world = n_ps + n_workers
     os.environ.setdefault("MASTER_ADDR", env.master_addr)

@@ -1,0 +1,39 @@
+"""Fused NVLink collectives vs the restated NCCL path on real GPUs (skipped on boxes with fewer than 2)."""
+import json
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run_dp_check(world: int, opt: str, port: int):
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", "gpu_dp_check.py"), opt]
+    p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    results = [json.loads(m) for m in re.findall(r'\{"rank": \d+.*?"ok": (?:true|false)\}', p.stdout)]
+    return p, results
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("opt", ["GD", "Adam"])
+def test_fused_collectives_two_ranks(opt):
+    """Replicas stay bit-identical and the update matches eager fp32 + NCCL (scripts/gpu_dp_check.py)."""
+    p, results = _run_dp_check(2, opt, 29631)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert len(results) == 2 and all(r["ok"] for r in results)
+    for r in results:
+        assert all(v for k, v in r.items() if k.startswith("identical:"))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 8, reason="needs 8 GPUs")
+def test_fused_collectives_eight_ranks():
+    p, results = _run_dp_check(8, "GD", 29632)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert len(results) == 8 and all(r["ok"] for r in results)
