@@ -38,14 +38,22 @@ LAYERS = (256, 128, 64)
 KEEP = (0.5, 0.5, 0.5)
 BATCH = 2048
 LR, L2 = 5e-4, 1e-4
+CONFIGS = {
+    "criteo": dict(feature=117581, emb=32, layers=(256, 128, 64),
+                   name="DeepFM F39 K32 V117581 MLP256-128-64 dropout0.5 Adam lazy-sparse"),
+    "large": dict(feature=33_000_000, emb=64, layers=(400, 400, 400),
+                  name="DeepFM F39 K64 V33M MLP400-400-400 dropout0.5 Adam lazy-sparse"),
+}
 POOL = 256          # distinct batches cycled through: 256 x 647 KB = 166 MB > the 126 MB L2
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=5000)
+    ap.add_argument("--warmup", type=int, default=100)
+    ap.add_argument("--config", default="criteo", choices=sorted(CONFIGS),
+                    help="criteo = BASELINE.json config 2 (the headline); large = config 3 (33M-row table, emb 64, MLP 400x3)")
     ap.add_argument("--impl", default="fused", choices=["fused", "reference", "eager"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--pool", type=int, default=POOL)
@@ -64,7 +72,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
             self.t.start()
@@ -103,7 +111,7 @@ def make_host_pool(batch: int, pool: int, rank: int, world: int):
     from deepfm_b200.data.loader import BatchLoader, alloc_slab
     from deepfm_b200.data.tfrecord import generate_synthetic
     n = batch * pool
-    path = os.path.join(tempfile.gettempdir(), f"dfm_bench_r{rank}_{n}.tfrecords")
+    path = os.path.join(tempfile.gettempdir(), f"dfm_bench_r{rank}_{n}_{FEATURE}.tfrecords")
     if not os.path.exists(path):
         generate_synthetic(path + ".tmp", n, FIELD, FEATURE, n_dense=13, seed=1234 + rank, pos_rate=0.2553, zipf_s=1.05)
         os.replace(path + ".tmp", path)
@@ -121,7 +129,9 @@ def make_host_pool(batch: int, pool: int, rank: int, world: int):
 
 
 def main():
+    global FEATURE, EMB, LAYERS
     args = parse_args()
+    FEATURE, EMB, LAYERS = CONFIGS[args.config]["feature"], CONFIGS[args.config]["emb"], CONFIGS[args.config]["layers"]
     if args.impl == "reference":
         print(json.dumps({"impl": "reference", "unavailable":
                           "reference is two TF1.14/1.15 + Horovod + sagemaker_tensorflow scripts with no setup.py; "
@@ -234,9 +244,11 @@ def main():
         "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16" if args.impl == "fused" else "fp32", "data": "synthetic",
         "impl": args.impl,
-        "config": {"model": "DeepFM F39 K32 V117581 MLP256-128-64 dropout0.5 Adam lazy-sparse",
+        "config": {"model": CONFIGS[args.config]["name"],
                    "global_batch": global_batch, "seq_len": FIELD, "parallelism": f"dp{world}",
-                   "l2": f"inputs rotate through {len(pool)} distinct batches ({len(pool) * slab_bytes / 1e6:.0f} MB > L2)",
+                   "l2": f"inputs rotate through {len(pool)} distinct batches ({len(pool) * slab_bytes / 1e6:.0f} MB"
+                         + (" > 126 MB L2)" if len(pool) * slab_bytes > 126e6 else
+                            "; the embedding tables touched per step exceed L2)" if FEATURE * EMB * 12 > 126e6 else ")"),
                    "backend": trainer.backend, "cuda_graph": trainer.uses_graph},
         "clocks": clocks,
         "e2e": {"value": e2e, "unit": "examples/s", "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": slab_bytes,

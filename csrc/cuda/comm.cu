@@ -137,8 +137,8 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   const OptStepConsts c = make_opt_consts(hyper, a.st);
   const unsigned int epoch = unsigned(a.st->comm_epoch);       // bumped by the first kernel of the step
   const int N = cv.world, Ke = a.Ke;
-  const int wp = cv.row_pitch;                         // 32-bit words per wire record
-  const int hw = Ke / 2;                               // words holding bf16 gradient pairs; then gw (fp32), id
+  const int hw = Ke / 2;                               // 32-bit words of a record's bf16 gradient pairs
+  const size_t tail_off = size_t(N) * cv.cap * hw;     // words: the {first-order gradient fp32, id} pairs follow all gradients
   const int gp = g_pitch(Ke);                          // floats per row of the local gradient buffer G
   const float inv_n = 1.f / float(N);
   const int lane = threadIdx.x & 31;
@@ -183,8 +183,10 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
     for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += blockDim.x) local_sum(gq);
   }
   // ---------------- phase 0b: push my sparse records to every rank ----------------
-  // wire record = wp words: [hw words of bf16 pairs | first-order gradient fp32 | id]; bf16 on the wire halves
-  // the all-gather's NVLink bytes (the accumulation on the receiving side is fp32, in rank order).
+  // wire format, structure of arrays: grads[sender][slot][hw words of bf16 pairs] then tails[sender][slot]{first-order
+  // gradient fp32, id}.  The G records a warp moves per instruction are consecutive slots, so it writes 32*8
+  // contiguous bytes of gradients and G*8 of tails per destination -- whole sectors on the NVLink.  bf16 on the wire
+  // halves the all-gather's bytes (the accumulation on the receiving side is fp32, in rank order).
   // LPR = Ke/4 lanes serve one record (four columns each), so a warp moves G = 32/LPR records per instruction and
   // keeps kRows * G of them in flight.  Record s belongs to group s / G; group gi is handled by warp gi % warps
   // on EVERY rank and in every phase -- so the per-CTA barrier below covers exactly what a CTA reads afterwards.
@@ -218,11 +220,11 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
         *reinterpret_cast<float4*>(grow + 4 * sub) = make_float4(0.f, 0.f, 0.f, 0.f);
         const uint2 w2 = make_uint2(pack_bf16x2(x[j].x, x[j].y), pack_bf16x2(x[j].z, x[j].w));
         const uint2 tail = make_uint2(__float_as_uint(gw[j]), uint32_t(id[j]));
-        const size_t off = (size_t(cv.rank) * cv.cap + sidx[j]) * wp;
+        const size_t rec = size_t(cv.rank) * cv.cap + sidx[j];
         for (int r = 0; r < N; ++r) {
-          uint32_t* dst = reinterpret_cast<uint32_t*>(cv.base[r] + off_in_rows) + off;
-          *reinterpret_cast<uint2*>(dst + 2 * sub) = w2;
-          if (sub == 0) *reinterpret_cast<uint2*>(dst + hw) = tail;
+          uint32_t* dst = reinterpret_cast<uint32_t*>(cv.base[r] + off_in_rows);
+          *reinterpret_cast<uint2*>(dst + rec * hw + 2 * sub) = w2;
+          if (sub == 0) *reinterpret_cast<uint2*>(dst + tail_off + rec * 2) = tail;
         }
         if (sub == 0) { grow[Ke] = 0.f; a.slot_of[id[j]] = -1; }
       }
@@ -267,7 +269,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
     for (int gi = first_warp + wi; gi * G + gg < nr; gi += warps) {
       const int sr = gi * G + gg;
-      const int id = int(__ldcg(in_rows + (size_t(r) * cv.cap + sr) * wp + hw + 1));
+      const int id = int(__ldcg(in_rows + tail_off + (size_t(r) * cv.cap + sr) * 2 + 1));
       entry_of[size_t(id) * N + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(sr + 1);
     }
   }
@@ -340,7 +342,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       const int nr = __shfl_sync(0xffffffffu, nr_l, rr[j] & 31);
       const int sr = (k * warps + warp_g) * G + g;
       const bool on = lane_on && it < n_items && sr < nr;
-      id[j] = on ? int(__ldcg(in_rows + (size_t(rr[j]) * cv.cap + sr) * wp + hw + 1)) : -1;
+      id[j] = on ? int(__ldcg(in_rows + tail_off + (size_t(rr[j]) * cv.cap + sr) * 2 + 1)) : -1;
     }
 #pragma unroll
     for (int j = 0; j < kRows; ++j) {
@@ -368,13 +370,14 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       for (int q = 0; q < kCommMaxRanks; ++q) {             // rank order: identical sum on every replica
         const int e = __shfl_sync(0xffffffffu, ent[j], lane_on ? g * LPR + (q < LPR ? q : 0) : lane);
         if (own && q < N && e) {
-          const uint32_t* row = in_rows + (size_t(q) * cv.cap + (e - 1)) * wp;
+          const size_t rec = size_t(q) * cv.cap + (e - 1);
+          const uint32_t* row = in_rows + rec * hw;
           const uint2 w2 = __ldcg(reinterpret_cast<const uint2*>(row + 2 * sub));
           const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&w2.x);
           const __nv_bfloat162 b1 = *reinterpret_cast<const __nv_bfloat162*>(&w2.y);
           acc.x += __low2float(b0); acc.y += __high2float(b0);
           acc.z += __low2float(b1); acc.w += __high2float(b1);
-          if (sub == 0) accw += __uint_as_float(__ldcg(row + hw));
+          if (sub == 0) accw += __uint_as_float(__ldcg(in_rows + tail_off + rec * 2));
         }
       }
       if (own) {

@@ -445,7 +445,7 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   CommView& cv = E->cv;
   cv.world = world; cv.rank = rank;
   cv.cap = E->cfg.batch_max * E->cfg.field_size;
-  cv.row_pitch = round_up(E->cfg.embedding_size / 2 + 2, 8);   // 32-bit words per wire record (bf16 pairs, gw, id)
+  cv.row_pitch = E->cfg.embedding_size / 2 + 2;   // 32-bit words per wire record: bf16 pairs + {gw, id} (kept in two arrays)
   cv.ctas = 132;             // one 1024-thread CTA per SM, with slack: every rank's CTAs must all be resident
   auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
   size_t o = 0;

@@ -246,7 +246,7 @@ struct CommView {
   uint8_t* base[kCommMaxRanks];
   int world, rank;
   int cap;            // inbox rows per sender (= batch_max * field_size)
-  int row_pitch;      // 32-bit words per inbox record: Ke/2 bf16 pairs, first-order gradient (fp32), id; whole sectors
+  int row_pitch;      // 32-bit words per inbox record: Ke/2 bf16 pairs + {first-order gradient fp32, id}, stored as two arrays
   int ctas;           // grid of the exchange kernel: <= one CTA per SM, all co-resident
   size_t off_dP, off_flags, off_flags2, off_in_count, off_in_rows;
   // dP, in_count and in_rows exist twice and alternate with the step parity: a rank that is already pushing step

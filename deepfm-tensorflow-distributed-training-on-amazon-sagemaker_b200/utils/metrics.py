@@ -82,9 +82,9 @@ class StreamingAUC:
         pos = labels > 0.5
         np.add.at(self.hist[0], b[pos], 1)
         np.add.at(self.hist[1], b[~pos], 1)
-        if self._all is not None:
-            self._all[0].append(labels)
-            self._all[1].append(preds)
+        if self._all is not None:              # copies: callers pass views into ring buffers that are reused
+            self._all[0].append(labels.copy())
+            self._all[1].append(preds.copy())
 
     @property
     def keep_all_enabled(self) -> bool:

@@ -138,6 +138,13 @@ def test_auc_modes():
     for i in range(0, 20000, 1024):
         s.update(y[i:i + 1024], p[i:i + 1024])
     assert abs(s.result() - tf_auc_numpy(y, p)) < 1e-12 and abs(s.result_exact() - exact_auc(y, p)) < 1e-12
+    # callers hand in views of reused ring buffers: what was seen must not change when the buffer does
+    s2, buf_y, buf_p = StreamingAUC(), np.empty(1024, np.float32), np.empty(1024, np.float32)
+    for i in range(0, 20000, 1024):
+        n = min(1024, 20000 - i)
+        buf_y[:n], buf_p[:n] = y[i:i + n], p[i:i + n]
+        s2.update(buf_y[:n], buf_p[:n])
+    assert abs(s2.result_exact() - exact_auc(y, p)) < 1e-12
     # ties and degenerate inputs
     assert exact_auc(np.array([0, 1, 0, 1.0]), np.array([0.5, 0.5, 0.5, 0.5])) == 0.5
     assert np.isnan(exact_auc(np.ones(4), np.random.rand(4)))
