@@ -71,7 +71,14 @@ def ncu_summaries():
     want = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__registers_per_thread",
             "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
             "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
-            "smsp__inst_executed.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed"]
+            "smsp__inst_executed.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+            "lts__t_sector_hit_rate.pct", "lts__t_sectors_srcunit_tex_op_red.sum", "launch__waves_per_multiprocessor",
+            "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_warps",
+            "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_sleeping_per_issue_active.ratio",
+            "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio"]
     for rep in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", "*.ncu-rep"))):
         p = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
         rows = list(csv.reader(io.StringIO(p.stdout)))
@@ -88,7 +95,25 @@ def ncu_summaries():
                 w.writerow([r[i] if i is not None else "" for i in idx])
 
 
+def sass_listings():
+    """Full SASS of the kernels BASELINE.json asks to see: the fused collective kernel and one tcgen05 GEMM."""
+    txt = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
+    blocks = re.split(r"(?=\t\tFunction : )", txt)
+    for key, fname in (("exchange_apply_kernel", "sass_exchange_apply_kernel.txt"),
+                       ("mlp_layer_kernelILb0", "sass_mlp_layer_fwd_kernel.txt"),
+                       ("embed_bwd_kernel", "sass_embed_bwd_kernel.txt")):
+        for b in blocks:
+            if key in b.split("\n", 1)[0]:
+                lines = [re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", ln) for ln in b.splitlines()]
+                lines = [ln for ln in lines if ln.strip() and not re.fullmatch(r"\s*/\* 0x[0-9a-f]+ \*/", ln)]
+                lines = [re.sub(r"^\s*(/\*[0-9a-f]+\*/)\s+", r"\1 ", ln) for ln in lines]
+                with open(os.path.join(OUT, fname), "w") as f:
+                    f.write("cuobjdump -sass libdfm_cuda.so (sm_100a), encodings stripped\n" + "\n".join(lines) + "\n")
+                break
+
+
 if __name__ == "__main__":
+    sass_listings()
     sass_summary()
     ptxas_summary()
     ncu_summaries()
