@@ -202,6 +202,12 @@ def main():
         ph = ["start", "setup", "mma_issued", "staged", "acc_ready", "epilogue", "end"]
         print("embed_bwd CTA(0,0) us: " + "  ".join(f"{ph[i]}@{(int(kd[i]) - int(kd[0])) / 1e3:.1f}" for i in range(7)),
               file=sys.stderr, flush=True)
+        S = 2 * (len(LAYERS) - 1)
+        t1 = int(kd[384])
+        if t1 > 0:
+            print("mid kernel stages (A ready, MMAs issued, acc ready, epilogue done) us: " + " | ".join(
+                " ".join(f"{(int(kd[384 + 4 * s + i]) - t1) / 1e3:.2f}" for i in range(4)) for s in range(S)),
+                file=sys.stderr, flush=True)
         n_cta = 80
         st = [int(kd[8 + 2 * i]) for i in range(n_cta)]
         en = [int(kd[9 + 2 * i]) for i in range(n_cta)]
