@@ -219,3 +219,38 @@ def test_fused_middle_matches_per_layer_kernels(monkeypatch):
     for k, width in (("act2", 128), ("act3", 64)):                    # rows past the batch are never written
         pitch = (width + 1 + 15) // 16 * 16
         assert torch.equal(outs[0][k].view(-1, pitch)[:300, :width], outs[1][k].view(-1, pitch)[:300, :width]), k
+
+
+def test_train_batches_pipelines_the_loader(tmp_path):
+    """Trainer.train_batches (look-ahead + in-graph prefetch + deferred slot release) == one batch at a time."""
+    from deepfm_b200.data.loader import BatchLoader
+    from deepfm_b200.data.tfrecord import generate_synthetic
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.runtime.trainer import Trainer, TrainerOptions
+    path = str(tmp_path / "tr.tfrecords")
+    generate_synthetic(path, 256 * 9 + 100, 39, 20000, n_dense=13, seed=3)
+    cfg = DeepFMConfig(39, 20000, 32, (256, 128, 64), (1.0, 1.0, 1.0), l2_reg=1e-4)
+    init = DeepFM(cfg, seed=2)
+    dev = torch.device("cuda", 0)
+    res = []
+    for pipelined in (True, False):
+        # plain SGD: Adam would turn summation-order noise on near-zero gradients into lr-sized differences
+        tr = Trainer(cfg, TrainerOptions(batch_size=256, optimizer="GD", learning_rate=0.05, backend="fused", seed=1),
+                     device=dev, init_model=init)
+        loader = BatchLoader([path], 39, 256, num_epochs=2, drop_remainder=True, num_workers=2, num_slots=4)
+        n = 0
+        if pipelined:
+            for _hb in tr.train_batches(loader):
+                n += 1
+        else:
+            for hb in loader:
+                tr.train_batch(hb)
+                torch.cuda.synchronize()        # the slot is reused as soon as the next batch is requested
+                n += 1
+        loader.close()
+        assert n == 18 and tr.global_step == 18
+        res.append(({k: v.detach().clone() for k, v in tr.variables().items()}, tr.last_loss(wait_current=True)))
+        tr.close()
+    assert abs(res[0][1] - res[1][1]) < 1e-4
+    for k in res[0][0]:
+        torch.testing.assert_close(res[0][0][k], res[1][0][k], rtol=2e-3, atol=5e-5, msg=k)
