@@ -22,7 +22,9 @@ dist.init_process_group("nccl", device_id=dev)
 
 B, F, V, K = 512, 39, 20000, 4
 opt = sys.argv[1] if len(sys.argv) > 1 else "GD"
-cfg = DeepFMConfig(F, V, 32, (256, 128, 64), (1.0, 1.0, 1.0), l2_reg=1e-3)
+KE = int(os.environ.get("DFM_DP_KE", "32"))          # other embedding sizes exercise other lane groupings of the exchange
+LAYERS = tuple(int(x) for x in os.environ.get("DFM_DP_LAYERS", "256,128,64").split(","))
+cfg = DeepFMConfig(F, V, KE, LAYERS, (1.0,) * len(LAYERS), l2_reg=1e-3)
 init = DeepFM(cfg, seed=3)
 with torch.no_grad():
     init.fm_v.mul_(20); init.fm_w.mul_(20)
@@ -40,7 +42,7 @@ def batches():
 
 data = batches()
 lr = 0.05 if opt == "GD" else 0.002
-res = {"rank": rank, "world": world, "opt": opt}
+res = {"rank": rank, "world": world, "opt": opt, "ke": KE}
 
 fused = Trainer(cfg, TrainerOptions(batch_size=B, optimizer=opt, learning_rate=lr, backend="fused", seed=3,
                                     cuda_graph=True), device=dev, init_model=init)

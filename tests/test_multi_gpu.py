@@ -12,8 +12,8 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _run_dp_check(world: int, opt: str, port: int):
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+def _run_dp_check(world: int, opt: str, port: int, **extra_env):
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", **extra_env)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", "gpu_dp_check.py"), opt]
     p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
@@ -30,6 +30,15 @@ def test_fused_collectives_two_ranks(opt):
     assert len(results) == 2 and all(r["ok"] for r in results)
     for r in results:
         assert all(v for k, v in r.items() if k.startswith("identical:"))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("ke", ["16", "64"])
+def test_fused_collectives_other_embedding_sizes(ke):
+    """Ke/4 lanes serve one record in the exchange kernel: 4 and 16 lanes per record, and a 400-400 MLP."""
+    p, results = _run_dp_check(2, "GD", 29633, DFM_DP_KE=ke, DFM_DP_LAYERS="400,400")
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert len(results) == 2 and all(r["ok"] for r in results)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 8, reason="needs 8 GPUs")
