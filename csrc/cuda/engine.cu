@@ -306,14 +306,15 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   // update run beside them on the side stream, behind dedupe
   DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork, s));
   DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork, 0));
-  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_dedupe, 0));
-  if ((rc = launch_embed_bwd(E.fmaps, bp, c.batch_max, s))) return rc;
-
+  // wgrad is queued first: its grid is sized to what embed_bwd leaves free (or to a third of the GPU when
+  // embed_bwd alone would fill it), and it heads the longer dependent chain of the two on wide networks
   WgradParams wp{};
   wp.sh = E.sh;
   for (int l = 0; l <= E.sh.L; ++l) wp.dP[l] = E.dP + E.off[l];
   wp.items = E.items; wp.st = E.st; wp.part_stride = E.part_stride;
   if ((rc = launch_wgrad(E.wmaps, wp, E.n_items, E.side))) return rc;
+  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_dedupe, 0));
+  if ((rc = launch_embed_bwd(E.fmaps, bp, c.batch_max, s))) return rc;
   const float gscale = 1.f;
   // (the dense update leaves the bf16 copy of W_0 alone -- embed_bwd's GEMM may still be reading it; see W0Cast)
   if (!E.comm_ready &&

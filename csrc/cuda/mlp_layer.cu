@@ -211,11 +211,16 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // prob, dlogit) is written by exactly one warp in one instruction:
 //   y_d = h_L . w_out + b_out ; logit ; prob ; BCE ; dlogit ;
 //   dz_{L-1} = (h_L > 0) * dlogit * w_out / keep_{L-1} ; dz_L = [dlogit, 0 ...].
+// LPE lanes per example (4, 8, 16 or 32, chosen from the width of the last hidden layer): with 4 lanes a warp
+// covers eight examples and writes one 32-byte sector of logit / prob / dlogit per instruction, but a 400-wide
+// layer then costs 13 dependent 16-byte loads per lane (17 us measured); wider layers get more lanes per example.
+template <int LPE>
 __global__ void __launch_bounds__(256)
 loss_init_kernel(const LossParams p) {
+  constexpr int EPW = 32 / LPE;                             // examples per warp
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int sub = lane >> 2, part = lane & 3;               // example within the warp, quarter of its row
-  const int b = (blockIdx.x * 8 + warp) * 8 + sub;
+  const int sub = lane / LPE, part = lane % LPE;            // example within the warp, slice of its row
+  const int b = (blockIdx.x * 8 + warp) * EPW + sub;
   const int count = p.st->count;
   pdl_launch_dependents();
   pdl_wait();
@@ -226,7 +231,7 @@ loss_init_kernel(const LossParams p) {
   const __nv_bfloat16* h = p.h_last + size_t(valid ? b : 0) * p.h_pitch;
   float yd = 0.f;
   if (valid)
-    for (int c = part * 8; c < p.n_last; c += 32) {          // 8 consecutive columns (16 bytes) per lane
+    for (int c = part * 8; c < p.n_last; c += 8 * LPE) {     // 8 consecutive columns (16 bytes) per lane
       const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + c));
       const uint32_t w4[4] = {hv.x, hv.y, hv.z, hv.w};
 #pragma unroll
@@ -236,8 +241,8 @@ loss_init_kernel(const LossParams p) {
         if (c + 2 * i + 1 < p.n_last) yd += __high2float(v) * __ldg(p.w_out + c + 2 * i + 1);
       }
     }
-  yd += __shfl_xor_sync(0xffffffffu, yd, 1);
-  yd += __shfl_xor_sync(0xffffffffu, yd, 2);
+#pragma unroll
+  for (int o = 1; o < LPE; o <<= 1) yd += __shfl_xor_sync(0xffffffffu, yd, o);
   float dl = 0.f;
   if (valid) {
     const float z = __ldg(p.fm_part + b) + yd + __ldg(p.w_out + p.n_last);
@@ -258,7 +263,7 @@ loss_init_kernel(const LossParams p) {
     const bool drop = p.st->train && p.keep_last < 1.f;
     const float scale = drop ? 1.f / p.keep_last : 1.f;
     __nv_bfloat16* dz = p.dz_last + size_t(b) * p.n_last;
-    for (int c = part * 8; c < p.n_last; c += 32) {
+    for (int c = part * 8; c < p.n_last; c += 8 * LPE) {
       uint4 hv = make_uint4(0u, 0u, 0u, 0u);
       if (valid) hv = __ldg(reinterpret_cast<const uint4*>(h + c));
       const uint32_t w4[4] = {hv.x, hv.y, hv.z, hv.w};
@@ -308,7 +313,12 @@ int launch_mlp_layer(bool backward, const CUtensorMap& tmA, const CUtensorMap& t
 }
 
 int launch_loss_init(const LossParams& p, int rows_pad, cudaStream_t stream) {
-  DFM_CUDA_CHECK(launch_pdl(kPdlLoss, loss_init_kernel, dim3(ceil_div(rows_pad, 64)), dim3(256), 0, stream, p));
+  const int lpe = p.n_last <= 64 ? 4 : p.n_last <= 128 ? 8 : p.n_last <= 256 ? 16 : 32;
+  const dim3 grid(ceil_div(rows_pad, 8 * (32 / lpe)));
+  if (lpe == 4)       DFM_CUDA_CHECK(launch_pdl(kPdlLoss, loss_init_kernel<4>, grid, dim3(256), 0, stream, p));
+  else if (lpe == 8)  DFM_CUDA_CHECK(launch_pdl(kPdlLoss, loss_init_kernel<8>, grid, dim3(256), 0, stream, p));
+  else if (lpe == 16) DFM_CUDA_CHECK(launch_pdl(kPdlLoss, loss_init_kernel<16>, grid, dim3(256), 0, stream, p));
+  else                DFM_CUDA_CHECK(launch_pdl(kPdlLoss, loss_init_kernel<32>, grid, dim3(256), 0, stream, p));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }
