@@ -62,12 +62,25 @@ __device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
   asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ uint2 ld_volatile_u2(const uint32_t* p) {
+  uint2 v;
+  asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ int ld_volatile_i(const int* p) {
   int v;
   asm volatile("ld.volatile.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 
+// caller picks the thread (CTA 0 only)
+__device__ __forceinline__ void stamp_any(const CommView& cv, int slot) {
+  if (blockIdx.x == 0 && cv.dbg) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    cv.dbg[slot] = t;
+  }
+}
 __device__ __forceinline__ void stamp(const CommView& cv, int slot) {
   if (blockIdx.x == 0 && threadIdx.x == 0 && cv.dbg) {
     unsigned long long t;
@@ -142,9 +155,20 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   const int gp = g_pitch(Ke);                          // floats per row of the local gradient buffer G
   const float inv_n = 1.f / float(N);
   const int lane = threadIdx.x & 31;
-  const int wpc = blockDim.x >> 5;
+  // Two warp groups (cv.split): the first 8 warps own the dense side (local split-K sum, then all-reduce + optimizer),
+  // the other 24 the sparse side (push, index, merge).  The two sides are independent after the cross-GPU barrier
+  // -- one is bound by NVLink reads, the other by random HBM rows -- so they run side by side instead of one after
+  // the other.  Without the split every thread does both jobs in turn (needed by the two-shot dense variant).
+  const bool split = cv.split != 0;
+  const int s0 = split ? 256 : 0;                      // first thread of the sparse group
+  const int ts = int(threadIdx.x) - s0;                // index inside the sparse group (< 0: dense-only thread)
+  const bool in_s = ts >= 0;
+  const int s_threads = int(blockDim.x) - s0;
+  const int d_threads = split ? 256 : int(blockDim.x);
+  const bool in_d = int(threadIdx.x) < d_threads;
+  const int wpc = s_threads >> 5;                      // sparse-side warps per CTA
   const int warps = gridDim.x * wpc;
-  const int warp_g = blockIdx.x * wpc + (threadIdx.x >> 5);
+  const int warp_g = blockIdx.x * wpc + (max(ts, 0) >> 5);
   const int n_mine = a.st->n_unique;
 
   // dense work split: CTA b owns float4 groups [g_lo, g_hi) of the gradient vector on every rank
@@ -172,15 +196,18 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       const float4 v = *reinterpret_cast<const float4*>(d.part + size_t(k) * d.part_stride + 4 * size_t(gq));
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
-    *reinterpret_cast<float4*>(my_dP + 4 * size_t(gq)) = acc;
+    if (cv.dense_bf16)   // wire format of the one-shot all-reduce: 4 bf16 = 8 bytes per group (half the NVLink bytes)
+      *reinterpret_cast<uint2*>(my_dP + 2 * size_t(gq)) = make_uint2(pack_bf16x2(acc.x, acc.y), pack_bf16x2(acc.z, acc.w));
+    else
+      *reinterpret_cast<float4*>(my_dP + 4 * size_t(gq)) = acc;
   };
   if (cv.two_shot) {
     for (int q = 0; q < N; ++q) {
       const int lo = q * c4 + blockIdx.x * per2, hi = min(min(lo + per2, (q + 1) * c4), n4);
       for (int gq = lo + threadIdx.x; gq < hi; gq += blockDim.x) local_sum(gq);
     }
-  } else {
-    for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += blockDim.x) local_sum(gq);
+  } else if (in_d) {
+    for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += d_threads) local_sum(gq);
   }
   // ---------------- phase 0b: push my sparse records to every rank ----------------
   // wire format, structure of arrays: grads[sender][slot][hw words of bf16 pairs] then tails[sender][slot]{first-order
@@ -194,7 +221,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   const int LPR = Ke >> 2, G = 32 / LPR;
   const int g = lane / LPR, sub = lane - g * LPR;
   const bool lane_on = g < G;
-  {
+  if (in_s) {
     const int n_groups = (n_mine + G - 1) / G;
     for (int gi0 = warp_g; gi0 < n_groups; gi0 += warps * kRows) {
       int sidx[kRows], id[kRows];
@@ -230,9 +257,9 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       }
     }
   }
-  if (threadIdx.x < N)
-    reinterpret_cast<int*>(cv.base[threadIdx.x] + off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n_mine;
-  stamp(cv, 1);
+  if (in_s && ts < N)
+    reinterpret_cast<int*>(cv.base[ts] + off_in_count)[cv.rank * kCommMaxCtas + blockIdx.x] = n_mine;
+  if (ts == 0) stamp_any(cv, 1);
   cta_barrier_all_ranks(cv, epoch);
   stamp(cv, 2);
 
@@ -263,7 +290,8 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
   const int* in_count = reinterpret_cast<const int*>(cv.base[cv.rank] + off_in_count);
   const uint32_t* in_rows = reinterpret_cast<const uint32_t*>(cv.base[cv.rank] + off_in_rows);
   const int first_warp = blockIdx.x * wpc;
-  for (int t = threadIdx.x; t < N * wpc * G; t += blockDim.x) {
+  auto index_phase = [&]() {
+  for (int t = ts; t < N * wpc * G; t += s_threads) {
     const int r = t / (wpc * G), u = t - r * (wpc * G);
     const int wi = u / G, gg = u - wi * G;
     const int nr = ld_volatile_i(in_count + r * kCommMaxCtas + blockIdx.x);
@@ -273,8 +301,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       entry_of[size_t(id) * N + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(sr + 1);
     }
   }
-  stamp(cv, 3);
-  grid_arrive(grid_bar);
+  };
 
   // ---------------- phase 1c: dense optimizer on the averaged gradient ----------------
   auto apply_group = [&](int gq, const float4& sum) {
@@ -294,6 +321,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       }
     }
   };
+  auto dense_phase = [&]() {
   if (cv.two_shot) {
     // the sums of my namesake CTAs' sub-slices (one per rank's chunk) have landed in my dP once their flags are up
     cta_wait_all_ranks(cv, cv.off_flags2, epoch);
@@ -304,20 +332,54 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
     }
   } else {
     // one-shot all-reduce: every rank reads all N copies of its groups
-    for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += blockDim.x) {
+    for (int gq = g_lo + threadIdx.x; gq < g_hi; gq += d_threads) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 4
       for (int q = 0; q < N; ++q) {                    // rank order: identical sum on every replica
-        const float4 v = ld_volatile_f4(reinterpret_cast<const float*>(cv.base[q] + off_dP) + 4 * size_t(gq));
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        const float* src = reinterpret_cast<const float*>(cv.base[q] + off_dP);
+        if (cv.dense_bf16) {                           // every rank, the owner included, adds the rounded values
+          const uint2 w = ld_volatile_u2(reinterpret_cast<const uint32_t*>(src + 2 * size_t(gq)));
+          const __nv_bfloat162 b0 = *reinterpret_cast<const __nv_bfloat162*>(&w.x);
+          const __nv_bfloat162 b1 = *reinterpret_cast<const __nv_bfloat162*>(&w.y);
+          acc.x += __low2float(b0); acc.y += __high2float(b0); acc.z += __low2float(b1); acc.w += __high2float(b1);
+        } else {
+          const float4 v = ld_volatile_f4(src + 4 * size_t(gq));
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
       }
       apply_group(gq, acc);
     }
   }
-  // (sits between the grid barrier's arrive and wait: it hides the barrier and the index phase's imbalance)
-  stamp(cv, 4);
-  grid_wait(cv, grid_bar, epoch);
-  stamp(cv, 5);
+  };
+
+  if (split) {
+    if (!in_s) {                                       // dense group: done after its phase (no CTA-wide barrier follows)
+      dense_phase();
+      stamp(cv, 4);
+      return;
+    }
+    index_phase();
+    if (ts == 0) stamp_any(cv, 3);
+    // grid barrier among the sparse groups of this GPU's CTAs (named barrier: the dense warps are not part of it)
+    asm volatile("bar.sync 1, 768;" ::: "memory");
+    if (ts == 0) {
+      red_release_gpu_add(grid_bar, 1u);
+      const unsigned int target = epoch * gridDim.x;
+      const long long t0 = clock64();
+      while (ld_acquire_gpu(grid_bar) < target)
+        if (clock64() - t0 > kCommWatchdog) comm_watchdog_trip(cv.rank, 1, -1, epoch);
+    }
+    asm volatile("bar.sync 1, 768;" ::: "memory");
+    if (ts == 0) stamp_any(cv, 5);
+  } else {
+    index_phase();
+    stamp(cv, 3);
+    grid_arrive(grid_bar);
+    dense_phase();     // sits between the grid barrier's arrive and wait: it hides the barrier and the index imbalance
+    stamp(cv, 4);
+    grid_wait(cv, grid_bar, epoch);
+    stamp(cv, 5);
+  }
 
   // ---------------- phase 2: owners merge and apply ----------------
   // Work items of a warp: (sender r, round k) -> group k*warps + warp_g of sender r; kRows items in flight.  Each
@@ -396,8 +458,7 @@ exchange_apply_kernel(const __grid_constant__ CommView cv, const SparseArgs a, c
       }
     }
   }
-  stamp(cv, 6);
-  kstamp(a.st, kStampSparseEnd);
+  if (ts == 0) { stamp_any(cv, 6); kstamp_any(a.st, kStampSparseEnd); }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -485,8 +485,13 @@ extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_han
   cv.off_in_count = o;  o += 2 * cv.in_count_bytes;
   cv.off_in_rows = o;   o += 2 * cv.in_rows_bytes;
   {
+    const char* sp = getenv("DFM_XCHG_SPLIT");
+    const char* w = getenv("DFM_DENSE_WIRE");
+    cv.dense_bf16 = w ? (strcmp(w, "bf16") == 0) : 0;
     const char* v = getenv("DFM_DENSE_TWO_SHOT");
     cv.two_shot = v ? atoi(v) : 0;   // measured on 2, 4 and 8 B200s: the one-shot form is 6-8 us faster per step
+    if (cv.two_shot) cv.dense_bf16 = 0;
+    cv.split = cv.two_shot ? 0 : (sp ? atoi(sp) : 1);
   }
   E->symm_bytes = o;
   void* p = nullptr;

@@ -290,6 +290,8 @@ struct CommView {
   // k+1 never writes what a slower peer may still be reading for step k (it cannot get two steps ahead: it needs
   // that peer's step-k+1 flag first)
   size_t dP_bytes, in_count_bytes, in_rows_bytes;
+  int split;          // dense side on 8 warps, sparse side on 24, side by side (not with two_shot)
+  int dense_bf16;     // one-shot dense all-reduce reads bf16 copies of the per-rank gradients (DFM_DENSE_WIRE=bf16|fp32)
   int two_shot;       // dense all-reduce as reduce-scatter + all-gather instead of one-shot (DFM_DENSE_TWO_SHOT=1)
   unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
 };
