@@ -254,3 +254,39 @@ def test_train_batches_pipelines_the_loader(tmp_path):
     assert abs(res[0][1] - res[1][1]) < 1e-4
     for k in res[0][0]:
         torch.testing.assert_close(res[0][0][k], res[1][0][k], rtol=2e-3, atol=5e-5, msg=k)
+
+
+def test_training_on_the_bundled_data_reaches_the_eager_auc(tmp_path, val_tfrecords):
+    """SURVEY section 4, integration level: train on 80% of val.tfrecords, evaluate on the rest; the fused bf16 engine
+    and the eager fp32 oracle must both learn (AUC well above 0.5) and agree."""
+    import copy
+    from deepfm_b200.data import tfrecord as T
+    from deepfm_b200.data.loader import BatchLoader
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.runtime.trainer import Trainer, TrainerOptions
+    recs = list(T.iter_records(val_tfrecords))
+    cut = int(len(recs) * 0.8)
+    paths = {}
+    for name, part in (("tr", recs[:cut]), ("va", recs[cut:])):
+        paths[name] = str(tmp_path / f"{name}.tfrecords")
+        with T.TFRecordWriter(paths[name]) as w:
+            for r in part:
+                w.write(r)
+    cfg = DeepFMConfig(39, 117581, 32, (256, 128, 64), (0.5, 0.5, 0.5), l2_reg=1e-4)
+    init = DeepFM(cfg, seed=1)
+    aucs = {}
+    for backend in ("eager", "fused"):
+        tr = Trainer(cfg, TrainerOptions(batch_size=256, optimizer="Adam", learning_rate=5e-4, backend=backend, seed=1),
+                     device=torch.device("cuda", 0), init_model=copy.deepcopy(init))
+        for _ in range(3):
+            loader = BatchLoader([paths["tr"]], 39, 256, num_epochs=1, drop_remainder=True, num_workers=2, num_slots=6)
+            for _hb in tr.train_batches(loader):
+                pass
+            loader.close()
+        loader = BatchLoader([paths["va"]], 39, 256, num_epochs=1, drop_remainder=False, num_workers=2)
+        aucs[backend] = tr.evaluate(loader, auc_mode="both")
+        loader.close()
+        tr.close()
+    assert aucs["eager"]["auc"] > 0.68 and aucs["fused"]["auc"] > 0.68, aucs
+    assert abs(aucs["eager"]["auc"] - aucs["fused"]["auc"]) < 0.02, aucs
+    assert abs(aucs["fused"]["auc"] - aucs["fused"]["auc_exact"]) < 0.01, aucs
