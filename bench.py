@@ -139,6 +139,8 @@ def main():
                           "(see DESIGN.md, BASELINE.md section 2)"}))
         return 0
 
+    # stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG is set on some boxes) goes to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import torch
     import torch.distributed as dist
 
