@@ -139,8 +139,11 @@ def main():
                           "(see DESIGN.md, BASELINE.md section 2)"}))
         return 0
 
-    # stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG is set on some boxes) goes to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries exactly one JSON line: while the benchmark runs, file descriptor 1 points at stderr, so what C
+    # libraries print (NCCL's version banner when NCCL_DEBUG is set on the box) cannot land in front of it
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
 
@@ -265,10 +268,13 @@ def main():
         "final_loss": final_loss, "mean_loss": loss_acc / max(K, 1),
         "loader_records_per_sec": parse_rate,
     }
-    if rank == 0:
-        print(json.dumps(out))
+    trainer.close()
     if world > 1:
         dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
     return 0
 
 
