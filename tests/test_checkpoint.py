@@ -70,3 +70,26 @@ def test_manager_keeps_last_n_and_resumes(tmp_path):
     step, r = ck.CheckpointManager(d).restore_latest()
     assert step == 30 and np.array_equal(r["fm_v"], t["fm_v"]) and "global_step" not in r
     assert ck.CheckpointManager(str(tmp_path / "empty")).restore_latest() is None
+
+
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@settings(max_examples=40, deadline=None)
+@given(seed=st.integers(0, 2 ** 31), n_vars=st.integers(1, 60))
+def test_bundle_roundtrip_property(tmp_path_factory, seed, n_vars):
+    """Any set of names (shared prefixes stress the SSTable's key compression), ranks 0-3, f32 / i64 / i32: identity."""
+    rng = np.random.default_rng(seed)
+    stems = ["a", "a/b", "a/b/c", "Deep-part/mlp", "Deep-part/mlp0/weights", "fm_v", "z" * 40]
+    t = {}
+    for i in range(n_vars):
+        name = f"{stems[int(rng.integers(len(stems)))]}{int(rng.integers(0, 10 ** int(rng.integers(1, 6))))}"
+        shape = tuple(int(x) for x in rng.integers(1, 7, int(rng.integers(0, 4))))
+        dt = [np.float32, np.int64, np.int32][int(rng.integers(3))]
+        t[name] = (rng.standard_normal(shape) * 100).astype(dt)
+    prefix = str(tmp_path_factory.mktemp("b") / "model.ckpt-7")
+    ck.write_bundle(prefix, t)
+    r = ck.read_bundle(prefix)
+    assert set(r) == set(t)
+    for k in t:
+        assert r[k].dtype == t[k].dtype and r[k].shape == t[k].shape and np.array_equal(r[k], t[k]), k

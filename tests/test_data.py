@@ -178,3 +178,61 @@ def test_synthetic_generator_is_criteo_shaped(tmp_path):
     assert 2000 < uniq < 40000       # skewed: far fewer distinct ids than 2048*39 lookups
     ids2, _, _ = T.read_all(f, 39)
     assert (ids2 == ids).all()
+
+
+# ---------------------------------------------------------------- property tests (hypothesis)
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@settings(max_examples=150, deadline=None)
+@given(n=st.integers(1, 64), packed=st.booleans(), seed=st.integers(0, 2 ** 31), label=st.sampled_from([0.0, 1.0, 0.5]))
+def test_example_codec_roundtrip_property(n, packed, seed, label):
+    """encode -> parse is the identity for any field count, id magnitude and encoding."""
+    rng = np.random.default_rng(seed)
+    ids = rng.integers(0, 2 ** 62, n)
+    vals = rng.standard_normal(n).astype(np.float32)
+    lab, i2, v2 = T.parse_example(T.encode_example(label, ids, vals, packed=packed), n)
+    assert lab == np.float32(label) and (i2 == ids).all() and (v2 == vals).all()
+
+
+@settings(max_examples=300, deadline=None)
+@given(seed=st.integers(0, 2 ** 31), n_flips=st.integers(1, 8), cut=st.integers(0, 40))
+def test_example_parser_survives_corruption(seed, n_flips, cut):
+    """A damaged payload is either rejected with DataError or parsed into well-formed arrays -- never a crash."""
+    rng = np.random.default_rng(seed)
+    payload = bytearray(T.encode_example(1.0, rng.integers(0, 10 ** 6, 39), rng.random(39).astype(np.float32),
+                                         packed=bool(seed & 1)))
+    for _ in range(n_flips):
+        payload[int(rng.integers(0, len(payload)))] = int(rng.integers(0, 256))
+    data = bytes(payload[: len(payload) - cut]) if cut else bytes(payload)
+    try:
+        lab, ids, vals = T.parse_example(data, 39)
+    except T.DataError:
+        return
+    assert ids.shape == (39,) and vals.shape == (39,) and np.isfinite(lab) | np.isnan(lab) | np.isinf(lab)
+
+
+@settings(max_examples=25, deadline=None)
+@given(seed=st.integers(0, 2 ** 31), n=st.integers(1, 300), batch=st.integers(1, 64), workers=st.integers(1, 4),
+       shard_n=st.integers(1, 3))
+def test_loader_delivers_every_record_once_in_order(tmp_path_factory, seed, n, batch, workers, shard_n):
+    """Whatever the batch size, worker count and shard: the loader yields exactly the shard's records, in file order."""
+    d = tmp_path_factory.mktemp("prop")
+    path = str(d / "x.tfrecords")
+    rng = np.random.default_rng(seed)
+    labels = rng.integers(0, 2, n).astype(np.float32)
+    first_ids = rng.integers(1, 10 ** 6, n)
+    with T.TFRecordWriter(path) as w:
+        for i in range(n):
+            ids = np.full(5, first_ids[i]); ids[1:] = np.arange(4)
+            w.write(T.encode_example(float(labels[i]), ids, np.ones(5, np.float32), packed=bool(i & 1)))
+    from deepfm_b200.data.loader import BatchLoader
+    for shard_i in range(shard_n):
+        got = []
+        loader = BatchLoader([path], 5, batch, num_epochs=1, drop_remainder=False, shard_n=shard_n, shard_i=shard_i,
+                             num_workers=workers, num_slots=3, ids_dtype=torch.int64, pin_memory=False)
+        for hb in loader:
+            got.extend(zip(hb.feat_ids[:, 0].tolist(), hb.labels.tolist()))
+        loader.close()
+        want = [(int(first_ids[i]), float(labels[i])) for i in range(n) if i % shard_n == shard_i]
+        assert got == want
