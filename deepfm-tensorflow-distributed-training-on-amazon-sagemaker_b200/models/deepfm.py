@@ -98,9 +98,11 @@ class DeepFM(nn.Module):
 
     # ------------------------------------------------------------------ forward
     def fm_terms(self, feat_ids: torch.Tensor, feat_vals: torch.Tensor):
-        w = self.fm_w[feat_ids]
+        # embedding_lookup (HVD.py:197,201); F.embedding rather than advanced indexing: same values, a far cheaper
+        # CPU gather and an index_add backward
+        w = F.embedding(feat_ids, self.fm_w.unsqueeze(1)).squeeze(-1)
         y_w = (w * feat_vals).sum(1)
-        e = self.fm_v[feat_ids] * feat_vals.unsqueeze(-1)
+        e = F.embedding(feat_ids, self.fm_v) * feat_vals.unsqueeze(-1)
         y_v = 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)
         return y_w, y_v, e
 
@@ -131,8 +133,8 @@ class DeepFM(nn.Module):
         the rows of the batch's distinct ids and ``inverse[B, F]`` indexes into them.  Differentiating
         w.r.t. the rows yields the de-duplicated sparse gradient directly."""
         feat_vals = feat_vals.float().view(-1, self.cfg.field_size)
-        y_w = (w_rows[inverse] * feat_vals).sum(1)
-        e = v_rows[inverse] * feat_vals.unsqueeze(-1)
+        y_w = (F.embedding(inverse, w_rows.unsqueeze(1)).squeeze(-1) * feat_vals).sum(1)
+        e = F.embedding(inverse, v_rows) * feat_vals.unsqueeze(-1)
         y_v = 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)
         return self._tower(y_w, y_v, e, training)
 

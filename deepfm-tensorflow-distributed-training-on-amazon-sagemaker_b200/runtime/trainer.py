@@ -326,8 +326,8 @@ class Trainer:
         m, opt, cfg = self.model, self.optimizer, self.cfg
         ids = ids.long()
         uniq, inverse = ids.unique(return_inverse=True)
-        w_rows = m.fm_w.detach()[uniq].requires_grad_(True)
-        v_rows = m.fm_v.detach()[uniq].requires_grad_(True)
+        w_rows = m.fm_w.detach().index_select(0, uniq).requires_grad_(True)
+        v_rows = m.fm_v.detach().index_select(0, uniq).requires_grad_(True)
         dense = [(n, p) for n, p in m.trainable_tf_variables().items() if n not in ("fm_w", "fm_v")]
         for _, p in dense:
             p.grad = None
@@ -343,8 +343,8 @@ class Trainer:
             for name, p in dense:
                 opt.apply_dense(name, p.data, p.grad)
             if self.opts.table_update_mode == "lazy":
-                opt.apply_rows("fm_w", m.fm_w.data, uniq, gw + cfg.l2_reg * m.fm_w.data[uniq])
-                opt.apply_rows("fm_v", m.fm_v.data, uniq, gv + cfg.l2_reg * m.fm_v.data[uniq])
+                opt.apply_rows("fm_w", m.fm_w.data, uniq, gw + cfg.l2_reg * m.fm_w.data.index_select(0, uniq))
+                opt.apply_rows("fm_v", m.fm_v.data, uniq, gv + cfg.l2_reg * m.fm_v.data.index_select(0, uniq))
             else:
                 dw = cfg.l2_reg * m.fm_w.data
                 dv = cfg.l2_reg * m.fm_v.data

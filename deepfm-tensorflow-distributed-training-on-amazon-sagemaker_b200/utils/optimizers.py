@@ -109,15 +109,16 @@ class TFOptimizer:
     def apply_rows(self, var: str, p: torch.Tensor, rows: torch.Tensor, g_rows: torch.Tensor) -> None:
         """Lazy sparse update: ``rows`` are distinct indices into dim 0 of ``p``."""
         s0, s1 = self.ensure_slots(var, p)
-        pr = p[rows]
-        r0 = s0[rows] if s0 is not None else None
-        r1 = s1[rows] if s1 is not None else None
+        rows = rows.long()
+        pr = p.index_select(0, rows)
+        r0 = s0.index_select(0, rows) if s0 is not None else None
+        r1 = s1.index_select(0, rows) if s1 is not None else None
         self._apply(pr, g_rows, r0, r1)
-        p[rows] = pr
+        p.index_copy_(0, rows, pr)
         if s0 is not None:
-            s0[rows] = r0
+            s0.index_copy_(0, rows, r0)
         if s1 is not None:
-            s1[rows] = r1
+            s1.index_copy_(0, rows, r1)
 
     def finish_step(self) -> None:
         self.step += 1
