@@ -197,10 +197,7 @@ class Loader {
             bw->recs.reserve(B);
             if (stable) bw->maps.push_back(src);
           }
-          {
-            std::lock_guard<std::mutex> l(mu_);
-            if (stop_) return;
-          }
+          // (stop / failure are noticed in submit(), once per batch: no lock per record on the reader's path)
         }
         bytes_ += static_cast<int64_t>(src->bytes_consumed());
         if (r < 0) {
