@@ -27,16 +27,18 @@ __device__ __forceinline__ void cast_w0(const W0Cast& wc) {
   if ((wc.n & 1) && blockIdx.x == 0 && threadIdx.x == 0) wc.dst[wc.n - 1] = __float2bfloat16(wc.src[wc.n - 1]);
 }
 
-constexpr int kMaxKPerLane = 4;   // embedding_size <= 128
-
-template <int KPL>   // embedding components per lane: embedding_size <= 32*KPL
+// Ke/4 lanes per table row (float4 each), so one load instruction of a warp gathers 32/(Ke/4) rows and U of them
+// put U*32/(Ke/4) rows in flight: all 39 fields of a Criteo example in ONE round trip at Ke = 32 (a lane-per-column
+// version needed five dependent rounds of eight).
+// Feature ids outside [0, V) are clamped into the table (every kernel that touches ids does the same, so the step
+// stays memory-safe) and counted in StepState::bad_ids for the host to report.
+template <int U>
 __global__ void __launch_bounds__(kEmbedWarps * 32)
-embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
-                    const float* __restrict__ fm_w, const float* __restrict__ fm_v,
-                    const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
-                    float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
-                    StepState* __restrict__ st, int* __restrict__ slot_of, int* __restrict__ uniq_ids,
-                    int dedupe, const W0Cast wc) {
+embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
+                       const float* __restrict__ fm_w, const float* __restrict__ fm_v,
+                       const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
+                       float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
+                       StepState* __restrict__ st, int dedupe, const W0Cast wc, int V) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kEmbedWarps + warp;
   const int count = st->count;
@@ -45,122 +47,13 @@ embed_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
   cast_w0(wc);
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->loss_sum = 0.f;            // accumulated by the loss kernel of this step
-    if (dedupe) {                  // == training step: open optimizer step (see StepState::step)
+    if (dedupe) {                  // == training step: open the optimizer step (see StepState::step)
       st->step += 1;
       st->comm_epoch += 1;
       open_step_consts(st);
       st->n_unique = 0;            // counted by dedupe, which is queued behind this kernel
-      st->n_union = 0;             // counted by the multi-GPU claim pass
-    }
-  }
-  // the 8 examples of a CTA are one 32-byte sector of fm_part: staged in smem, stored by one thread
-  __shared__ __align__(16) float part_out[kEmbedWarps];
-  const bool active = b < count;
-  if (active) {
-  const int* my_ids = ids + size_t(b) * F;
-  const float* my_vals = vals + size_t(b) * F;
-
-  float S[KPL], Q[KPL];
 #pragma unroll
-  for (int j = 0; j < KPL; ++j) S[j] = Q[j] = 0.f;
-  float yw = 0.f;
-
-  for (int f0 = 0; f0 < F; f0 += 32) {
-    const int nf = min(32, F - f0);
-    int id_l = 0;
-    float x_l = 0.f;
-    if (lane < nf) {
-      id_l = __ldg(my_ids + f0 + lane);
-      x_l = __ldg(my_vals + f0 + lane);
-      yw += __ldg(fm_w + id_l) * x_l;
-    }
-    // U fields in flight per iteration: independent 128 B row gathers (the kernel is latency-bound)
-    constexpr int U = KPL == 1 ? 8 : 4;
-    for (int f = 0; f < nf; f += U) {
-      float row[U][KPL];
-      float xs[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int ff = min(f + u, nf - 1);
-        const int id = __shfl_sync(0xffffffffu, id_l, ff);
-        xs[u] = __shfl_sync(0xffffffffu, x_l, ff);
-        const float* src = fm_v + size_t(id) * Ke;
-#pragma unroll
-        for (int j = 0; j < KPL; ++j) {
-          const int k = lane + 32 * j;
-          row[u][j] = k < Ke ? __ldg(src + k) : 0.f;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (f + u < nf) {
-          __nv_bfloat16* dst = e + size_t(b) * pitch + size_t(f0 + f + u) * Ke;
-#pragma unroll
-          for (int j = 0; j < KPL; ++j) {
-            const int k = lane + 32 * j;
-            if (k < Ke) {
-              const float ev = row[u][j] * xs[u];
-              S[j] += ev;
-              Q[j] += ev * ev;
-              dst[k] = __float2bfloat16(ev);
-            }
-          }
-        }
-      }
-    }
-  }
-
-  float yv = 0.f;
-#pragma unroll
-  for (int j = 0; j < KPL; ++j) {
-    const int k = lane + 32 * j;
-    if (k < Ke) {
-      yv += S[j] * S[j] - Q[j];
-      s_sum[size_t(b) * Ke + k] = S[j];
-    }
-  }
-  float tot = yw + 0.5f * yv;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-  if (lane == 0) part_out[warp] = tot + __ldg(fm_bias);
-  }  // active
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const int b0 = blockIdx.x * kEmbedWarps;
-    if (b0 + kEmbedWarps <= count) {
-      float4* dst = reinterpret_cast<float4*>(fm_part + b0);
-      dst[0] = make_float4(part_out[0], part_out[1], part_out[2], part_out[3]);
-      dst[1] = make_float4(part_out[4], part_out[5], part_out[6], part_out[7]);
-    } else {
-      for (int i = 0; b0 + i < count; ++i) fm_part[b0 + i] = part_out[i];
-    }
-  }
-}
-
-// Same pass with Ke/4 lanes per table row (float4 each), so one load instruction of a warp gathers 32/(Ke/4)
-// rows and U of them put U*32/(Ke/4) rows in flight: all 39 fields of a Criteo example in ONE round trip at
-// Ke = 32, where the scalar kernel above needed five dependent rounds of eight.  Used when Ke % 4 == 0.
-template <int U>
-__global__ void __launch_bounds__(kEmbedWarps * 32)
-embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ vals,
-                       const float* __restrict__ fm_w, const float* __restrict__ fm_v,
-                       const float* __restrict__ fm_bias, __nv_bfloat16* __restrict__ e, int pitch,
-                       float* __restrict__ s_sum, float* __restrict__ fm_part, int F, int Ke,
-                       StepState* __restrict__ st, int dedupe, const W0Cast wc) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int b = blockIdx.x * kEmbedWarps + warp;
-  const int count = st->count;
-  pdl_launch_dependents();     // the first MLP layer may be scheduled now; it waits for this grid before reading
-  kstamp(st, kStampEmbedFwd);
-  cast_w0(wc);
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    st->loss_sum = 0.f;
-    if (dedupe) {
-      st->step += 1;
-      st->comm_epoch += 1;
-      open_step_consts(st);
-      st->n_unique = 0;
-      st->n_union = 0;
+      for (int o = 0; o < 8; ++o) st->n_seg[o] = 0;
     }
   }
   __shared__ __align__(16) float part_out[kEmbedWarps];
@@ -180,7 +73,12 @@ embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ va
       for (int u = 0; u < U; ++u) {
         const int f = f0 + u * G + g;
         const bool on = lane_on && f < F;
-        id[u] = on ? __ldg(my_ids + f) : -1;
+        id[u] = -1;
+        if (on) {
+          const int raw = __ldg(my_ids + f);
+          id[u] = min(max(raw, 0), V - 1);
+          if (raw != id[u]) atomicAdd(&st->bad_ids, 1);
+        }
         x[u] = on ? __ldg(my_vals + f) : 0.f;
       }
       float4 row[U];
@@ -249,7 +147,7 @@ constexpr int kDedupeHash = 2048;                    // >= 2x threads per CTA, p
 
 __global__ void __launch_bounds__(1024)
 dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, int* __restrict__ slot_of,
-              int* __restrict__ uniq_ids) {
+              int* __restrict__ uniq_ids, int world, int cap, int V) {
   const int total = st->count * F;
   kstamp(st, kStampDedupe);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -258,13 +156,15 @@ dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, in
   __shared__ unsigned char tab_multi[kDedupeHash]; // the id was inserted more than once in this CTA
   __shared__ int warp_base[32];
   __shared__ int cta_base;
+  __shared__ int seg_cnt[8], seg_base[8];          // multi-GPU: winners of this CTA per owner rank
+  if (threadIdx.x < 8) seg_cnt[threadIdx.x] = 0;
   for (int t = threadIdx.x; t < kDedupeHash; t += blockDim.x) { tab_id[t] = -1; tab_multi[t] = 0; }
   __syncthreads();
 
   int id = 0, h = 0;
   bool leader = false;
   if (i < total) {
-    id = __ldg(ids + i);
+    id = min(max(__ldg(ids + i), 0), V - 1);       // out-of-range ids: clamped, like everywhere else in the step
     h = int((unsigned(id) * 2654435761u) >> 21) & (kDedupeHash - 1);
     while (true) {
       const int prev = atomicCAS(&tab_id[h], -1, id);
@@ -282,6 +182,25 @@ dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, in
     if (v == -1) v = atomicCAS(&slot_of[id], -1, pre);
     if (v == -1) won = 1;
     else if (!slot_multi(v)) atomicOr(&slot_of[id], kSlotMulti);   // another CTA holds it: the id repeats
+  }
+
+  if (world > 1) {
+    // Multi-GPU: the slot space has one segment per owner rank (owner = id % world, segment o = slots
+    // [o * cap, (o + 1) * cap)), so the records the exchange kernel streams to one owner are contiguous.
+    // Winners count per owner in shared memory; one returning global atomic per owner per CTA.
+    const int o = id % world;
+    int pos = 0;
+    if (won) pos = atomicAdd(&seg_cnt[o], 1);
+    __syncthreads();
+    if (threadIdx.x < world)
+      seg_base[threadIdx.x] = seg_cnt[threadIdx.x] ? atomicAdd(&st->n_seg[threadIdx.x], seg_cnt[threadIdx.x]) : 0;
+    __syncthreads();
+    if (won) {
+      const int s = o * cap + seg_base[o] + pos;
+      uniq_ids[s] = id;
+      atomicOr(&slot_of[id], s + 1);     // keeps a multi flag that arrived while the slot was being allocated
+    }
+    return;
   }
 
   // one counter bump per CTA: returning atomics on a single address serialise at ~50 ns each
@@ -307,9 +226,12 @@ dedupe_kernel(const int* __restrict__ ids, int F, StepState* __restrict__ st, in
   }
 }
 
-int launch_dedupe(const int* ids, int F, StepState* st, int* slot_of, int* uniq_ids, int batch_max,
-                  cudaStream_t stream) {
-  dedupe_kernel<<<ceil_div(batch_max * F, 1024), 1024, 0, stream>>>(ids, F, st, slot_of, uniq_ids);
+int launch_dedupe(const int* ids, int F, StepState* st, int* slot_of, int* uniq_ids, int batch_max, int world, int cap,
+                  long long V, cudaStream_t stream) {
+  DFM_REQUIRE(V > 0 && V <= 0x7fffffffLL, "dedupe: feature_size %lld does not fit int32 ids", V);
+  DFM_REQUIRE(world >= 1 && world <= 8 && (world == 1 || (long long)world * cap < kSlotMulti),
+              "dedupe: %d ranks x %d slots exceed the slot encoding", world, cap);
+  dedupe_kernel<<<ceil_div(batch_max * F, 1024), 1024, 0, stream>>>(ids, F, st, slot_of, uniq_ids, world, cap, int(V));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }
@@ -323,32 +245,21 @@ __global__ void fill_ones_column_kernel(__nv_bfloat16* act, int rows, int pitch,
 
 int launch_embed_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v,
                         const float* fm_bias, __nv_bfloat16* e, int pitch, float* s_sum, float* fm_part,
-                        int F, int Ke, int batch_max, StepState* st, int* slot_of, int* uniq_ids,
-                        int dedupe, W0Cast wc, cudaStream_t stream) {
+                        int F, int Ke, int batch_max, StepState* st, int dedupe, W0Cast wc, long long V,
+                        cudaStream_t stream) {
   DFM_REQUIRE((reinterpret_cast<uintptr_t>(wc.src) & 7) == 0 && (reinterpret_cast<uintptr_t>(wc.dst) & 3) == 0,
               "W_0 cast: misaligned buffers");
-  DFM_REQUIRE(Ke <= 32 * kMaxKPerLane, "embedding_size %d > %d is not supported", Ke, 32 * kMaxKPerLane);
+  DFM_REQUIRE(Ke % 4 == 0 && Ke >= 8 && Ke <= 128 && pitch % 4 == 0, "embedding_size %d is not supported", Ke);
+  DFM_REQUIRE(V > 0 && V <= 0x7fffffffLL, "feature_size %lld does not fit int32 ids", V);
   const int grid = ceil_div(batch_max, kEmbedWarps);
-  if (Ke % 4 == 0 && Ke >= 8 && Ke <= 128 && pitch % 4 == 0) {
-    // rows in flight per warp = U * (32 / (Ke/4)); enough to cover F in one round when it fits in registers
-    const int G = 32 / (Ke / 4);
-    if (ceil_div(F, G) <= 10)
-      embed_fm_fwd_v4_kernel<10><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
-                                                                        fm_part, F, Ke, st, dedupe, wc);
-    else
-      embed_fm_fwd_v4_kernel<16><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
-                                                                        fm_part, F, Ke, st, dedupe, wc);
-    DFM_LAUNCH_CHECK();
-    return DFM_OK;
-  }
-#define DFM_EMBED_LAUNCH(KPL)                                                                          \
-  embed_fm_fwd_kernel<KPL><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, \
-                                                                  s_sum, fm_part, F, Ke, st, slot_of,   \
-                                                                  uniq_ids, dedupe, wc)
-  if (Ke <= 32) DFM_EMBED_LAUNCH(1);
-  else if (Ke <= 64) DFM_EMBED_LAUNCH(2);
-  else DFM_EMBED_LAUNCH(4);
-#undef DFM_EMBED_LAUNCH
+  // rows in flight per warp = U * (32 / (Ke/4)); enough to cover F in one round when it fits in registers
+  const int G = 32 / (Ke / 4);
+  if (ceil_div(F, G) <= 10)
+    embed_fm_fwd_v4_kernel<10><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
+                                                                      fm_part, F, Ke, st, dedupe, wc, int(V));
+  else
+    embed_fm_fwd_v4_kernel<16><<<grid, kEmbedWarps * 32, 0, stream>>>(ids, vals, fm_w, fm_v, fm_bias, e, pitch, s_sum,
+                                                                      fm_part, F, Ke, st, dedupe, wc, int(V));
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

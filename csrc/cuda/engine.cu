@@ -68,20 +68,19 @@ struct Engine {
   float* loss_ring = nullptr;                  // pinned [kPipe]
   const void* staged_src[kPipe] = {nullptr, nullptr};   // what the prefetch node last copied into each slab
 
-  // multi-GPU: symmetric block + peer mappings (see comm.cu)
-  CommView cv{};
-  uint8_t* symm = nullptr;
-  size_t symm_bytes = 0;
+  // multi-GPU: views of every rank's symmetric block and tables (see comm.cu)
+  XchgArgs xa{};
   bool comm_ready = false;
-  unsigned long long* entry_of = nullptr;     // [V, world] {epoch, row+1} of the record rank r sent for an id
-  unsigned int* grid_bar = nullptr;
+  bool emu = false;                           // single-GPU emulation of N ranks: the collectives are launched for all
+                                              // virtual ranks at once by dfm_engine_emu_collectives
+  XchgArgs* emu_args = nullptr;               // device array [emu_ranks] (owned by virtual rank 0)
+  int emu_ranks = 0;
   unsigned long long* comm_dbg = nullptr;
   unsigned long long* kern_dbg = nullptr;
   MidParams mid{};               // fused middle of the step (mlp_mid.cu); mid_smem < 0: not usable for this network
   int mid_smem = -1;
   bool mid_active = false;       // the current training pass went through the fused middle
   int dedupe_after = 0;          // forward layer after which dedupe is forked (-1: right after embed_fwd); DFM_DEDUPE_AFTER
-  std::vector<void*> peer_maps;
 
   template <typename T>
   int alloc(T** p, size_t n, int fill_byte = 0) {
@@ -228,10 +227,10 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   const MlpShape& sh = E.sh;
   int rc;
   const float* fm_bias = E.t.dense + E.off[sh.L + 1];
-  // embed_fm_fwd opens the step: it also clears the per-step counters (n_unique, n_union, loss_sum)
+  // embed_fm_fwd opens the step: it also clears the per-step counters (n_unique, n_seg, loss_sum)
   if ((rc = launch_embed_fm_fwd(ids, vals, E.t.fm_w, E.t.fm_v, fm_bias, E.act[0], sh.pitch[0], E.s_sum, E.fm_part,
-                                c.field_size, c.embedding_size, c.batch_max, E.st, E.slot_of, E.uniq_ids, train,
-                                W0Cast{E.t.dense + E.off[0], E.Wb + E.off[0], sh.K[0] * sh.N[0]}, s)))
+                                c.field_size, c.embedding_size, c.batch_max, E.st, train,
+                                W0Cast{E.t.dense + E.off[0], E.Wb + E.off[0], sh.K[0] * sh.N[0]}, c.feature_size, s)))
     return rc;
   // Sparse-gradient bookkeeping (dedupe) runs on the side stream beside the MLP; its results are first needed by
   // embed_bwd, which is queued behind it there.  It is forked after layer `dedupe_after` (default 0): next to the
@@ -240,7 +239,8 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   auto fork_dedupe = [&]() -> int {
     DFM_CUDA_CHECK(cudaEventRecord(E.ev_fork0, s));
     DFM_CUDA_CHECK(cudaStreamWaitEvent(E.side, E.ev_fork0, 0));
-    const int r = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max, E.side);
+    const int r = launch_dedupe(ids, c.field_size, E.st, E.slot_of, E.uniq_ids, c.batch_max,
+                                E.comm_ready ? E.xa.cv.world : 1, c.batch_max * c.field_size, c.feature_size, E.side);
     if (r) return r;
     DFM_CUDA_CHECK(cudaEventRecord(E.ev_dedupe, E.side));
     return DFM_OK;
@@ -278,6 +278,15 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   return launch_loss_init(q, train ? E.Bpad : c.batch_max, s);
 }
 
+static SparseArgs sparse_args(const Engine& E) {
+  SparseArgs sa{};
+  sa.fm_v = E.t.fm_v; sa.v_s0 = E.t.fm_v_s0; sa.v_s1 = E.t.fm_v_s1;
+  sa.fm_w = E.t.fm_w; sa.w_s0 = E.t.fm_w_s0; sa.w_s1 = E.t.fm_w_s1;
+  sa.G = E.G; sa.Gw = E.Gw; sa.slot_of = E.slot_of; sa.uniq_ids = E.uniq_ids; sa.st = E.st;
+  sa.Ke = E.cfg.embedding_size; sa.V = E.cfg.feature_size; sa.grad_scale = 1.f;
+  return sa;
+}
+
 static int engine_backward_update(Engine& E, const int* ids, const float* vals, cudaStream_t s) {
   const dfm_engine_config& c = E.cfg;
   BwdParams bp{};
@@ -289,7 +298,7 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   bp.w_out = E.t.dense + E.off[E.sh.L];
   bp.dlogit = E.dlogit; bp.st = E.st;
   bp.ids = ids; bp.vals = vals; bp.s_sum = E.s_sum; bp.slot_of = E.slot_of; bp.G = E.G; bp.Gw = E.Gw;
-  bp.F = c.field_size; bp.Ke = c.embedding_size; bp.dbg = E.kern_dbg;
+  bp.F = c.field_size; bp.Ke = c.embedding_size; bp.V = int(c.feature_size); bp.dbg = E.kern_dbg;
   int rc;
   for (int l = E.sh.L - 1; l >= 1 && !E.mid_active; --l) {       // dz_{l-1} = (h_l > 0) * (dz_l W_l^T) / keep_{l-1}
     LayerParams lp{};
@@ -316,26 +325,27 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_dedupe, 0));
   if ((rc = launch_embed_bwd(E.fmaps, bp, c.batch_max, s))) return rc;
   const float gscale = 1.f;
+  if (E.comm_ready) {
+    // Multi-GPU.  The dense all-reduce + optimizer follows the weight-gradient GEMM on the side stream and so runs
+    // under embed_bwd; the sparse exchange + owner-sharded update follows embed_bwd on the main stream.  In the
+    // single-GPU emulation both are launched once for all virtual ranks by dfm_engine_emu_collectives.
+    if (!E.emu && (rc = launch_dense_sync(E.xa, nullptr, 0, E.side))) return rc;
+    DFM_CUDA_CHECK(cudaEventRecord(E.ev_join, E.side));
+    if (!E.emu && (rc = launch_exchange_apply(E.xa, nullptr, 0, s))) return rc;
+    if (!E.emu && E.xa.cv.exact &&
+        (rc = launch_table_dense_from(sparse_args(E), E.hyper, E.xa.cv.tab_g[E.xa.cv.rank], 1.f / float(E.xa.cv.world), s)))
+      return rc;
+    DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
+    return DFM_OK;
+  }
   // (the dense update leaves the bf16 copy of W_0 alone -- embed_bwd's GEMM may still be reading it; see W0Cast)
-  if (!E.comm_ready &&
-      (rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride, E.Wb, E.n_dense, E.st,
+  if ((rc = launch_dense_opt(E.t.dense, E.t.dense_s0, E.t.dense_s1, E.dP, E.ksplit, E.part_stride, E.Wb, E.n_dense, E.st,
                              E.hyper, gscale, int(E.off[0]), int(E.off[0]) + E.sh.K[0] * E.sh.N[0], E.side)))
     return rc;
   DFM_CUDA_CHECK(cudaEventRecord(E.ev_join, E.side));
 
-  SparseArgs sa{};
-  sa.fm_v = E.t.fm_v; sa.v_s0 = E.t.fm_v_s0; sa.v_s1 = E.t.fm_v_s1;
-  sa.fm_w = E.t.fm_w; sa.w_s0 = E.t.fm_w_s0; sa.w_s1 = E.t.fm_w_s1;
-  sa.G = E.G; sa.Gw = E.Gw; sa.slot_of = E.slot_of; sa.uniq_ids = E.uniq_ids; sa.st = E.st;
-  sa.Ke = c.embedding_size; sa.V = c.feature_size; sa.grad_scale = gscale;
-  if (E.comm_ready) {
-    // multi-GPU: dense all-reduce + optimizer and the sparse exchange + lazy update in one kernel
-    DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
-    DenseArgs da{};
-    da.P = E.t.dense; da.s0 = E.t.dense_s0; da.s1 = E.t.dense_s1; da.part = E.dP; da.ksplit = E.ksplit;
-    da.part_stride = E.part_stride; da.Wb = E.Wb; da.n = E.n_dense;
-    return launch_exchange_apply(E.cv, sa, da, E.entry_of, E.grid_bar, E.hyper, s);
-  }
+  SparseArgs sa = sparse_args(E);
+  sa.grad_scale = gscale;
   rc = launch_sparse_apply(sa, E.hyper, c.batch_max * c.field_size, c.table_update_mode == DFM_TABLE_DENSE_EXACT, s);
   DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E.ev_join, 0));
   return rc;
@@ -365,7 +375,6 @@ extern "C" int dfm_engine_destroy(void* h) {
   if (!h) return DFM_OK;
   Engine* E = static_cast<Engine*>(h);
   cudaDeviceSynchronize();
-  for (void* p : E->peer_maps) cudaIpcCloseMemHandle(p);
   for (void* p : E->allocs) cudaFree(p);
   if (E->side) cudaStreamDestroy(E->side);
   if (E->ev_fork) cudaEventDestroy(E->ev_fork);
@@ -422,7 +431,7 @@ extern "C" int dfm_engine_launches_per_step(void* h) {
   // dedupe, embed_fwd, L forward layers, loss, L-1 backward layers, embed_bwd, wgrad, dense opt, sparse (1 or 2)
   // single GPU: + dense opt + sparse apply; multi GPU: + one exchange kernel
   const int mlp = E->mid_smem > 0 ? 2 /* first layer + fused middle */ : E->sh.L + 1 + (E->sh.L - 1);
-  return 2 + mlp + 2 + (E->comm_ready ? 1 : 2);
+  return 2 + mlp + 2 + 2;   // + dense optimizer + sparse apply (multi-GPU: dense all-reduce + sparse exchange)
 }
 
 // ---- phase timing (warm, CUDA events) ----------------------------------------------------------
@@ -458,76 +467,167 @@ extern "C" int dfm_engine_profile(void* h, const int* ids, const float* vals, co
 }
 
 // ---- multi-GPU attachment ---------------------------------------------------------------------
-// Step 1 (every rank): allocate the symmetric block and export it.
-extern "C" int dfm_engine_comm_alloc(void* h, int world, int rank, void* ipc_handle_out /* 64 bytes */) {
-  Engine* E = static_cast<Engine*>(h);
-  DFM_REQUIRE(world >= 2 && world <= kCommMaxRanks && rank >= 0 && rank < world, "comm: world %d rank %d unsupported",
-              world, rank);
-  DFM_REQUIRE(E->cfg.table_update_mode == DFM_TABLE_LAZY, "multi-GPU fused path implements the lazy table update");
-  DFM_REQUIRE(!E->symm, "comm already allocated");
-  // the merge phase gives one lane per sender out of the embedding_size/4 lanes that serve a record
-  DFM_REQUIRE(world <= E->cfg.embedding_size / 4, "multi-GPU fused path: world %d needs embedding_size >= %d", world,
-              4 * world);
-  CommView& cv = E->cv;
-  cv.world = world; cv.rank = rank;
-  cv.cap = E->cfg.batch_max * E->cfg.field_size;
-  cv.row_pitch = E->cfg.embedding_size / 2 + 2;   // 32-bit words per wire record: bf16 pairs + {gw, id} (kept in two arrays)
-  cv.ctas = 132;             // one 1024-thread CTA per SM, with slack: every rank's CTAs must all be resident
-  auto align = [](size_t x) { return (x + 255) & ~size_t(255); };
+// The caller (parallel/symmetric.py) owns the symmetric memory: it allocates, on every rank, one block of
+// dfm_engine_comm_bytes() zeroed bytes, makes every rank's block and embedding tables addressable from every rank
+// (torch symmetric memory with an NVLS multicast address, or CUDA IPC), and hands the pointers to comm_attach.
+static size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+static size_t comm_layout(const Engine& E, int world, CommView* cv) {
+  const size_t cap = size_t(E.cfg.batch_max) * E.cfg.field_size;
+  const size_t n4 = size_t(round_up(E.n_dense, 4)) + 8;
   size_t o = 0;
-  const size_t n4 = size_t(round_up(E->n_dense, 4)) + 8;
-  cv.dP_bytes = align(n4 * 4);
-  cv.in_count_bytes = align(size_t(world) * kCommMaxCtas * 4);
-  cv.in_rows_bytes = align(size_t(world) * cv.cap * cv.row_pitch * 4);
-  cv.off_dP = o;        o += 2 * cv.dP_bytes;
-  cv.off_flags = o;     o = align(o + size_t(world) * kCommMaxCtas * 4);
-  cv.off_flags2 = o;    o = align(o + size_t(world) * kCommMaxCtas * 4);
-  cv.off_in_count = o;  o += 2 * cv.in_count_bytes;
-  cv.off_in_rows = o;   o += 2 * cv.in_rows_bytes;
-  {
-    const char* sp = getenv("DFM_XCHG_SPLIT");
-    const char* w = getenv("DFM_DENSE_WIRE");
-    cv.dense_bf16 = w ? (strcmp(w, "bf16") == 0) : 0;
-    const char* v = getenv("DFM_DENSE_TWO_SHOT");
-    cv.two_shot = v ? atoi(v) : 0;   // measured on 2, 4 and 8 B200s: the one-shot form is 6-8 us faster per step
-    if (cv.two_shot) cv.dense_bf16 = 0;
-    cv.split = cv.two_shot ? 0 : (sp ? atoi(sp) : 1);
-  }
-  E->symm_bytes = o;
-  void* p = nullptr;
-  DFM_CUDA_CHECK(cudaMalloc(&p, o));
-  DFM_CUDA_CHECK(cudaMemset(p, 0, o));
-  E->allocs.push_back(p);
-  E->symm = static_cast<uint8_t*>(p);
-  cudaIpcMemHandle_t hd;
-  DFM_CUDA_CHECK(cudaIpcGetMemHandle(&hd, p));
-  static_assert(sizeof(hd) == 64, "IPC handle size");
-  memcpy(ipc_handle_out, &hd, 64);
-  int rc;
-  if ((rc = E->alloc(&E->entry_of, size_t(E->cfg.feature_size) * world))) return rc;
-  if ((rc = E->alloc(&E->grid_bar, 64))) return rc;
-  if ((rc = E->alloc(&E->comm_dbg, 32))) return rc;
-  cv.dbg = E->comm_dbg;
-  DFM_CUDA_CHECK(cudaDeviceSynchronize());
+  CommView tmp{};
+  CommView& v = cv ? *cv : tmp;
+  v.off_dP = o;        o = align256(o + n4 * 4);
+  v.flags_bytes = align256(size_t(world) * kCommMaxCtas * 4);
+  v.off_flags = o;     o += 4 * v.flags_bytes;
+  v.off_in_count = o;  o = align256(o + size_t(world) * kCommMaxCtas * 4);
+  v.off_in_tails = o;  o = align256(o + size_t(world) * cap * 8);
+  v.off_in_grads = o;  o = align256(o + size_t(world) * cap * E.cfg.embedding_size * 4);
+  return o;
+}
+
+extern "C" int dfm_engine_comm_bytes(void* h, int world, long long* bytes) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(world >= 2 && world <= kCommMaxRanks, "comm: world %d unsupported (2..%d)", world, kCommMaxRanks);
+  *bytes = (long long)comm_layout(*E, world, nullptr);
   return DFM_OK;
 }
 
-// Step 2 (every rank, after an all-gather of the handles): map the peers and switch the step to the
-// in-kernel collectives.  The local gradient buffer moves into the symmetric block.
-extern "C" int dfm_engine_comm_attach(void* h, const void* all_handles /* world x 64 bytes */) {
+// Buffers whose size depends on the world size, and the argument block of the collective kernels.
+static int comm_prepare(Engine& E, int world, int rank, int ctas, int dense_ctas) {
+  DFM_REQUIRE(world >= 2 && world <= kCommMaxRanks && rank >= 0 && rank < world, "comm: world %d rank %d unsupported",
+              world, rank);
+  DFM_REQUIRE(!E.comm_ready, "comm already attached");
+  // the merge phase gives one lane per sender out of the embedding_size/4 lanes that serve a record
+  DFM_REQUIRE(world <= E.cfg.embedding_size / 4, "multi-GPU fused path: world %d needs embedding_size >= %d", world,
+              4 * world);
+  DFM_REQUIRE(ctas >= world && ctas <= kCommMaxCtas && dense_ctas >= 1 && dense_ctas <= kCommMaxCtas, "comm: bad grid");
+  const size_t cap = size_t(E.cfg.batch_max) * E.cfg.field_size;
+  int rc;
+  // one slot segment per owner rank (dedupe_kernel): worst case every id of a batch has the same owner
+  if ((rc = E.alloc(&E.G, size_t(world) * cap * g_pitch(E.cfg.embedding_size)))) return rc;
+  if ((rc = E.alloc(&E.uniq_ids, size_t(world) * cap))) return rc;
+  XchgArgs& x = E.xa;
+  x = XchgArgs{};
+  if ((rc = E.alloc(&x.entry_of, size_t(E.cfg.feature_size) + world))) return rc;
+  if ((rc = E.alloc(&x.grid_bar, 64))) return rc;
+  if ((rc = E.alloc(&E.comm_dbg, 32))) return rc;
+  CommView& cv = x.cv;
+  comm_layout(E, world, &cv);
+  cv.world = world; cv.rank = rank; cv.cap = int(cap);
+  cv.ctas = ctas; cv.dense_ctas = dense_ctas;
+  cv.dbg = E.comm_dbg;
+  cv.exact = E.cfg.table_update_mode == DFM_TABLE_DENSE_EXACT;
+  double secs = 120.0;     // a rank may legitimately stall this long on the host (checkpoint, input) while its peers wait
+  if (const char* v = getenv("DFM_COMM_TIMEOUT_S")) secs = atof(v);
+  cv.watchdog = (long long)(std::max(secs, 0.001) * 1.9e9);
+  x.a = sparse_args(E);
+  x.d.P = E.t.dense; x.d.s0 = E.t.dense_s0; x.d.s1 = E.t.dense_s1; x.d.part = E.dP; x.d.ksplit = E.ksplit;
+  x.d.part_stride = E.part_stride; x.d.Wb = E.Wb; x.d.n = E.n_dense;
+  x.d.wb_skip_lo = int(E.off[0]); x.d.wb_skip_hi = int(E.off[0]) + E.sh.K[0] * E.sh.N[0];
+  x.hyper = E.hyper;
+  return DFM_OK;
+}
+
+// block_ptrs / fm_v_ptrs / fm_w_ptrs: `world` device pointers each (entry `rank` = this rank's own buffer); *_mc: the
+// NVLS multicast address of the same buffers or NULL.  grad_ptrs / grad_mc: only for the dense_exact table update
+// (per-rank [V, embedding_size + 8] fp32 zeroed tables that receive the summed sparse gradients), else NULL.
+extern "C" int dfm_engine_comm_attach(void* h, int world, int rank, void* const* block_ptrs, void* block_mc,
+                                      void* const* fm_v_ptrs, void* fm_v_mc, void* const* fm_w_ptrs, void* fm_w_mc,
+                                      void* const* grad_ptrs, void* grad_mc) {
   Engine* E = static_cast<Engine*>(h);
-  DFM_REQUIRE(E->symm, "call dfm_engine_comm_alloc first");
-  CommView& cv = E->cv;
-  for (int r = 0; r < cv.world; ++r) {
-    if (r == cv.rank) { cv.base[r] = E->symm; continue; }
-    cudaIpcMemHandle_t hd;
-    memcpy(&hd, static_cast<const uint8_t*>(all_handles) + 64 * r, 64);
-    void* p = nullptr;
-    DFM_CUDA_CHECK(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
-    E->peer_maps.push_back(p);
-    cv.base[r] = static_cast<uint8_t*>(p);
+  DFM_REQUIRE(block_ptrs && fm_v_ptrs && fm_w_ptrs, "dfm_engine_comm_attach: null pointer table");
+  int dense_ctas = 16;
+  if (const char* v = getenv("DFM_DENSE_CTAS")) dense_ctas = atoi(v);
+  // one 1024-thread CTA per SM, all resident at once, beside the dense kernel's CTAs
+  int rc = comm_prepare(*E, world, rank, 148 - dense_ctas, dense_ctas);
+  if (rc) return rc;
+  CommView& cv = E->xa.cv;
+  DFM_REQUIRE(fm_v_ptrs[rank] == E->t.fm_v && fm_w_ptrs[rank] == E->t.fm_w,
+              "dfm_engine_comm_attach: entry %d of the table pointers must be this engine's own fm_v / fm_w", rank);
+  DFM_REQUIRE(!cv.exact || grad_ptrs, "dense_exact on several GPUs needs the summed-gradient tables");
+  for (int r = 0; r < world; ++r) {
+    cv.base[r] = static_cast<uint8_t*>(block_ptrs[r]);
+    cv.tab_v[r] = static_cast<float*>(fm_v_ptrs[r]);
+    cv.tab_w[r] = static_cast<float*>(fm_w_ptrs[r]);
+    cv.tab_g[r] = grad_ptrs ? static_cast<float*>(grad_ptrs[r]) : nullptr;
   }
+  const char* no_mc = getenv("DFM_NO_MULTICAST");
+  const bool use_mc = !(no_mc && no_mc[0] == '1');
+  cv.mc_base = use_mc ? static_cast<uint8_t*>(block_mc) : nullptr;
+  // the tables take multicast stores only if both have an alias
+  const bool tab_mc = use_mc && fm_v_mc && fm_w_mc && (!cv.exact || grad_mc);
+  cv.mc_v = tab_mc ? static_cast<float*>(fm_v_mc) : nullptr;
+  cv.mc_w = tab_mc ? static_cast<float*>(fm_w_mc) : nullptr;
+  cv.mc_g = tab_mc && cv.exact ? static_cast<float*>(grad_mc) : nullptr;
   E->comm_ready = true;
+  return DFM_OK;
+}
+
+// 1 if the attached views use NVLS multicast for the dense all-reduce / for the table rows (bit 0 / bit 1)
+extern "C" int dfm_engine_comm_multicast(void* h) {
+  Engine* E = static_cast<Engine*>(h);
+  return (E->xa.cv.mc_base ? 1 : 0) | (E->xa.cv.mc_v ? 2 : 0);
+}
+
+// ---- single-GPU emulation of N ranks ---------------------------------------------------------
+// N engines on ONE device stand for N ranks: each runs its own forward / backward, and the two collective kernels
+// are launched once, cooperatively, over all virtual ranks' data (blockIdx.x / ctas = rank).  This is how the
+// multi-rank protocol is tested (and profiled under ncu) on a box with a single GPU; separate launches per rank that
+// wait on one another on one GPU would not be guaranteed to run at the same time.
+extern "C" int dfm_engine_emu_attach(void* const* engines, int n, void* const* grad_tables) {
+  DFM_REQUIRE(engines && n >= 2 && n <= kCommMaxRanks, "dfm_engine_emu_attach: 2..%d engines", kCommMaxRanks);
+  int dev = 0, sms = 0;
+  DFM_CUDA_CHECK(cudaGetDevice(&dev));
+  DFM_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int ctas = std::max(n, std::min(kCommMaxCtas, sms / n));     // all n * ctas CTAs must be co-resident
+  const int dense_ctas = std::max(1, std::min(16, sms / n));
+  std::vector<uint8_t*> blocks(n);
+  for (int r = 0; r < n; ++r) {
+    Engine* E = static_cast<Engine*>(engines[r]);
+    int rc = comm_prepare(*E, n, r, ctas, dense_ctas);
+    if (rc) return rc;
+    if ((rc = E->alloc(&blocks[r], comm_layout(*E, n, nullptr)))) return rc;
+  }
+  std::vector<XchgArgs> all(n);
+  for (int r = 0; r < n; ++r) {
+    Engine* E = static_cast<Engine*>(engines[r]);
+    CommView& cv = E->xa.cv;
+    DFM_REQUIRE(!cv.exact || grad_tables, "dense_exact emulation needs the summed-gradient tables");
+    for (int q = 0; q < n; ++q) {
+      Engine* Q = static_cast<Engine*>(engines[q]);
+      cv.base[q] = blocks[q];
+      cv.tab_v[q] = Q->t.fm_v;
+      cv.tab_w[q] = Q->t.fm_w;
+      cv.tab_g[q] = grad_tables ? static_cast<float*>(grad_tables[q]) : nullptr;
+    }
+    E->emu = true;
+    E->emu_ranks = n;
+    E->comm_ready = true;
+    all[r] = E->xa;
+  }
+  Engine* E0 = static_cast<Engine*>(engines[0]);
+  int rc = E0->alloc(&E0->emu_args, size_t(n));
+  if (rc) return rc;
+  DFM_CUDA_CHECK(cudaMemcpy(E0->emu_args, all.data(), sizeof(XchgArgs) * n, cudaMemcpyHostToDevice));
+  return DFM_OK;
+}
+
+// Call after dfm_engine_train_step of every virtual rank (same stream): the collectives of that step, all ranks.
+extern "C" int dfm_engine_emu_collectives(void* const* engines, int n, dfm_stream_t s_) {
+  Engine* E0 = static_cast<Engine*>(engines[0]);
+  DFM_REQUIRE(E0->emu && E0->emu_args && E0->emu_ranks == n, "dfm_engine_emu_collectives: call dfm_engine_emu_attach first");
+  cudaStream_t s = static_cast<cudaStream_t>(s_);
+  int rc = launch_dense_sync(E0->xa, E0->emu_args, n, s);
+  if (rc) return rc;
+  if ((rc = launch_exchange_apply(E0->xa, E0->emu_args, n, s))) return rc;
+  if (E0->cfg.table_update_mode == DFM_TABLE_DENSE_EXACT) {
+    for (int r = 0; r < n; ++r) {
+      Engine* E = static_cast<Engine*>(engines[r]);
+      if ((rc = launch_table_dense_from(sparse_args(*E), E->hyper, E->xa.cv.tab_g[r], 1.f / float(n), s))) return rc;
+    }
+  }
   return DFM_OK;
 }
 
@@ -744,9 +844,9 @@ extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** pt
   else if (!strcmp(name, "state")) { p = E->st; n = sizeof(StepState) / 4; }
   else if (!strcmp(name, "dense_grad")) { p = E->dP; n = (long long)E->part_stride * E->ksplit; }
   else if (!strcmp(name, "dense_bf16")) { p = E->Wb; n = E->n_dense; }
-  else if (!strcmp(name, "G")) { p = E->G; n = (long long)E->cfg.batch_max * E->cfg.field_size * g_pitch(E->cfg.embedding_size); }
+  else if (!strcmp(name, "G")) { p = E->G; n = (long long)(E->comm_ready ? E->xa.cv.world : 1) * E->cfg.batch_max * E->cfg.field_size * g_pitch(E->cfg.embedding_size); }
   else if (!strcmp(name, "Gw")) { p = E->Gw; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
-  else if (!strcmp(name, "uniq_ids")) { p = E->uniq_ids; n = (long long)E->cfg.batch_max * E->cfg.field_size; }
+  else if (!strcmp(name, "uniq_ids")) { p = E->uniq_ids; n = (long long)(E->comm_ready ? E->xa.cv.world : 1) * E->cfg.batch_max * E->cfg.field_size; }
   else if (!strcmp(name, "slot_of")) { p = E->slot_of; n = E->cfg.feature_size; }
   else if (!strcmp(name, "kern_dbg")) { p = E->kern_dbg; n = 1024; }
   else if (!strcmp(name, "comm_dbg")) { p = E->comm_dbg; n = 64; }   /* 32 x u64 phase timestamps, as int32 pairs */
@@ -771,5 +871,40 @@ extern "C" int dfm_engine_layout(void* h, long long* offsets, int* pitches, int*
   for (int l = 0; l <= E->sh.L; ++l) pitches[l] = E->sh.pitch[l];
   *n_dense = E->n_dense;
   *bpad = E->Bpad;
+  return DFM_OK;
+}
+
+// ---- plain device allocations + CUDA IPC (fallback symmetric-memory provider) ----------------
+extern "C" int dfm_dev_alloc(long long bytes, void** ptr) {
+  DFM_REQUIRE(bytes > 0 && ptr, "dfm_dev_alloc: bad arguments");
+  void* p = nullptr;
+  DFM_CUDA_CHECK(cudaMalloc(&p, size_t(bytes)));
+  DFM_CUDA_CHECK(cudaMemset(p, 0, size_t(bytes)));
+  *ptr = p;
+  return DFM_OK;
+}
+
+extern "C" int dfm_dev_free(void* ptr) {
+  if (ptr) DFM_CUDA_CHECK(cudaFree(ptr));
+  return DFM_OK;
+}
+
+extern "C" int dfm_ipc_export(const void* ptr, void* handle_out) {
+  DFM_REQUIRE(ptr && handle_out, "dfm_ipc_export: null argument");
+  cudaIpcMemHandle_t hd;
+  static_assert(sizeof(hd) == 64, "IPC handle size");
+  DFM_CUDA_CHECK(cudaIpcGetMemHandle(&hd, const_cast<void*>(ptr)));
+  memcpy(handle_out, &hd, 64);
+  return DFM_OK;
+}
+
+// The mapping stays open for the life of the process (the engines that use it do not own it).
+extern "C" int dfm_ipc_open(const void* handle, void** ptr) {
+  DFM_REQUIRE(handle && ptr, "dfm_ipc_open: null argument");
+  cudaIpcMemHandle_t hd;
+  memcpy(&hd, handle, 64);
+  void* p = nullptr;
+  DFM_CUDA_CHECK(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+  *ptr = p;
   return DFM_OK;
 }

@@ -27,9 +27,9 @@ struct StepState {
   float lr;           // learning rate (already multiplied by world size, HVD.py:171)
   float loss_sum;     // sum of per-example BCE over the batch (this rank)
   int n_unique;       // distinct table rows touched by the current batch
-  int sparse_done;    // (unused)
+  int bad_ids;        // feature ids outside [0, feature_size) seen so far (they are clamped; the host reports them)
   int train;          // 1: dropout active, gradients produced
-  int n_union;        // multi-GPU: distinct rows touched by any rank this step
+  int reserved1;
   int comm_epoch;     // multi-GPU: completed collective rounds (flag value of the next round = +1)
   float adam_b1, adam_b2;   // > 0 when the optimizer is Adam: the step's first kernel derives lr_t from them
   float lr_t;               // Adam: lr * sqrt(1 - b2^t) / (1 - b1^t) of the update in flight (one powf pair per step,
@@ -37,6 +37,9 @@ struct StepState {
   // %globaltimer when CTA 0 of each kernel of the last step started (slots: kStamp*); read by the
   // timeline probe (scripts/gpu_timeline.py) to see launch gaps inside the replayed graph
   unsigned long long kstamp[24];
+  // multi-GPU: distinct ids of the current batch owned by rank o (id % world == o); dedupe hands out the compact
+  // slots of owner o from segment o of the slot space, so the records that go to one owner are contiguous
+  int n_seg[8];
 };
 
 enum : int { kStampEmbedFwd = 0, kStampDedupe = 1, kStampFwd0 = 2, kStampLoss = 8, kStampBwd0 = 9, kStampEmbedBwd = 15,
@@ -182,6 +185,7 @@ struct BwdParams {
   float* G;                    // [slots, Ke]
   float* Gw;                   // [slots]
   int F, Ke;
+  int V;                       // feature_size: ids are clamped into [0, V)
   unsigned long long* dbg;     // optional phase timestamps (globaltimer ns) written by CTA (0,0)
 };
 
@@ -276,42 +280,59 @@ __host__ __device__ inline uint32_t mid_smem_bytes(uint32_t a_bytes, uint32_t w_
   return 2u * a_bytes + w_bytes + 256u + 1024u + 8192u + 1024u;
 }
 
-// Multi-GPU view of the symmetric blocks (one per rank, identical layout, peers mapped via CUDA IPC).
+// Multi-GPU view: every rank's symmetric block and embedding tables are addressable from every rank (peer mappings over
+// NVLink; optionally also through one NVLS multicast address that stores to / reduces over all of them).
+// Identical on all ranks except `rank`.
 constexpr int kCommMaxRanks = 8;
 constexpr int kCommMaxCtas = 160;
 struct CommView {
-  uint8_t* base[kCommMaxRanks];
+  uint8_t* base[kCommMaxRanks];      // symmetric block of rank r
+  uint8_t* mc_base;                  // multicast alias of all symmetric blocks (null: no NVLS; peers are looped over)
+  float* tab_v[kCommMaxRanks];       // fm_v of rank r
+  float* tab_w[kCommMaxRanks];       // fm_w of rank r
+  float* mc_v; float* mc_w;          // multicast aliases of the tables (null: none)
   int world, rank;
-  int cap;            // inbox rows per sender (= batch_max * field_size)
-  int row_pitch;      // 32-bit words per inbox record: Ke/2 bf16 pairs + {first-order gradient fp32, id}, stored as two arrays
-  int ctas;           // grid of the exchange kernel: <= one CTA per SM, all co-resident
-  size_t off_dP, off_flags, off_flags2, off_in_count, off_in_rows;
-  // dP, in_count and in_rows exist twice and alternate with the step parity: a rank that is already pushing step
-  // k+1 never writes what a slower peer may still be reading for step k (it cannot get two steps ahead: it needs
-  // that peer's step-k+1 flag first)
-  size_t dP_bytes, in_count_bytes, in_rows_bytes;
-  int split;          // dense side on 8 warps, sparse side on 24, side by side (not with two_shot)
-  int dense_bf16;     // one-shot dense all-reduce reads bf16 copies of the per-rank gradients (DFM_DENSE_WIRE=bf16|fp32)
-  int two_shot;       // dense all-reduce as reduce-scatter + all-gather instead of one-shot (DFM_DENSE_TWO_SHOT=1)
-  unsigned long long* dbg;   // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
+  int cap;            // inbox rows per sender and slots per owner segment (= batch_max * field_size)
+  int ctas;           // CTAs per rank of the sparse exchange kernel (all co-resident)
+  int dense_ctas;     // CTAs per rank of the dense all-reduce kernel
+  // symmetric block: dense gradient vector | 4 flag arrays [world][kCommMaxCtas] (dense round 1, 2; sparse round 1, 2)
+  // | inbox counts [world][kCommMaxCtas] | inbox gradients [world][cap][Ke] fp32 | inbox tails [world][cap]{gw, id}
+  size_t off_dP, off_flags, off_in_count, off_in_grads, off_in_tails;
+  size_t flags_bytes;                // one flag array
+  long long watchdog;                // clock64 ticks a cross-GPU or grid wait may take before the kernel traps
+  int exact;                         // dense_exact table update: the owner publishes summed gradient rows, not parameters
+  float* tab_g[kCommMaxRanks];       // dense_exact: per-rank [V, g_pitch] summed-gradient table
+  float* mc_g;
+  unsigned long long* dbg;           // 32 phase timestamps (globaltimer ns) written by CTA 0 of the collective kernels
 };
 
-// launchers (one per translation unit)
 struct DenseArgs {
   float* P; float* s0; float* s1;        // flat dense parameters and optimizer slots
   const float* part; int ksplit; size_t part_stride;   // split-K slices of the dense gradient
   __nv_bfloat16* Wb;
   int n;
+  int wb_skip_lo, wb_skip_hi;            // bf16 copy of W_0 is left to the next step's first kernel (see W0Cast)
 };
-int launch_exchange_apply(const CommView&, const SparseArgs&, const DenseArgs&, unsigned long long*, unsigned int*,
-                          const OptHyper&, cudaStream_t);
+
 // The bf16 copy of W_0 is refreshed by the FIRST kernel of the next pass (embed_fm_fwd), not by the dense optimizer
 // kernel: that one runs while embed_bwd's GEMM may still be reading W_0 through TMA.
 struct W0Cast { const float* src; __nv_bfloat16* dst; int n; };
+// Everything the two collective kernels need.  A real rank passes its own block by value; the single-GPU
+// emulation of N ranks (one cooperative launch over all ranks' data) passes an array indexed by virtual rank.
+struct XchgArgs {
+  CommView cv;
+  SparseArgs a;
+  DenseArgs d;
+  unsigned long long* entry_of;          // [V + world] {epoch, slot+1} of the record sender r pushed for an owned id
+  unsigned int* grid_bar;
+  OptHyper hyper;
+};
+int launch_dense_sync(const XchgArgs&, const XchgArgs* emu, int emu_ranks, cudaStream_t);
+int launch_exchange_apply(const XchgArgs&, const XchgArgs* emu, int emu_ranks, cudaStream_t);
 int launch_embed_fm_fwd(const int*, const float*, const float*, const float*, const float*, __nv_bfloat16*, int,
-                        float*, float*, int, int, int, StepState*, int*, int*, int, W0Cast, cudaStream_t);
+                        float*, float*, int, int, int, StepState*, int, W0Cast, long long V, cudaStream_t);
 int launch_fill_ones_column(__nv_bfloat16*, int, int, int, cudaStream_t);
-int launch_dedupe(const int*, int, StepState*, int*, int*, int, cudaStream_t);
+int launch_dedupe(const int*, int, StepState*, int*, int*, int, int world, int cap, long long V, cudaStream_t);
 int mlp_layer_set_smem();
 int launch_mlp_layer(bool, const CUtensorMap&, const CUtensorMap&, const LayerParams&, int, cudaStream_t);
 int launch_loss_init(const LossParams&, int, cudaStream_t);
@@ -327,5 +348,6 @@ int launch_dense_opt(float*, float*, float*, const float*, int, size_t, __nv_bfl
                      const OptHyper&, float, int wb_skip_lo, int wb_skip_hi, cudaStream_t);
 int launch_cast_weights(const float*, __nv_bfloat16*, int, cudaStream_t);
 int launch_sparse_apply(const SparseArgs&, const OptHyper&, int, bool, cudaStream_t);
+int launch_table_dense_from(const SparseArgs&, const OptHyper&, float* gsum, float inv_n, cudaStream_t);
 
 }  // namespace dfm

@@ -143,7 +143,7 @@ embed_bwd_kernel(const __grid_constant__ FwdMaps maps, const __grid_constant__ B
         const int j = j_lo + jj;
         const int f = gcol(j * Ke) / Ke;
         const bool on = valid && jj < (nf >> 1) && f < F;
-        idv[jj] = on ? __ldg(p.ids + size_t(b) * F + f) : -1;
+        idv[jj] = on ? min(max(__ldg(p.ids + size_t(b) * F + f), 0), p.V - 1) : -1;
         xv[jj] = on ? __ldg(p.vals + size_t(b) * F + f) : 0.f;
       }
       int sl[kEbMaxFields / 2];

@@ -137,6 +137,35 @@ table_dense_kernel(const SparseArgs a, const OptHyper hyper) {
   }
 }
 
+// dense_exact on several GPUs: the owner of each touched row has published the row's gradient summed over all ranks
+// into every replica's `gsum` table ([V, g_pitch], zero elsewhere); every replica then sweeps its whole table with
+// g = gsum / N + l2 * row -- the reference's math (HVD.py:266-267) -- and clears what it consumed.
+__global__ void __launch_bounds__(256)
+table_dense_from_kernel(const SparseArgs a, const OptHyper hyper, float* __restrict__ gsum, float inv_n) {
+  const OptStepConsts c = make_opt_consts(hyper, a.st);
+  const int lane = threadIdx.x & 31;
+  const int gp = g_pitch(a.Ke);
+  const long long warps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long id = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; id < a.V; id += warps) {
+    float* grow = gsum + size_t(id) * gp;
+    for (int k = lane; k < a.Ke; k += 32) {
+      const size_t pi = size_t(id) * a.Ke + k;
+      float p = a.fm_v[pi], m = a.v_s0[pi], v = a.v_s1[pi];
+      const float gs = grow[k];
+      if (gs != 0.f) grow[k] = 0.f;
+      opt_apply(c, hyper.l2_reg * p + gs * inv_n, p, m, v);
+      a.fm_v[pi] = p; a.v_s0[pi] = m; a.v_s1[pi] = v;
+    }
+    if (lane == 0) {
+      float p = a.fm_w[id], m = a.w_s0[id], v = a.w_s1[id];
+      const float gs = grow[a.Ke];
+      if (gs != 0.f) grow[a.Ke] = 0.f;
+      opt_apply(c, hyper.l2_reg * p + gs * inv_n, p, m, v);
+      a.fm_w[id] = p; a.w_s0[id] = m; a.w_s1[id] = v;
+    }
+  }
+}
+
 // ---- streaming AUC accumulators, tf.metrics.auc(num_thresholds=200) (HVD.py:271) ----
 // bucket(p) = number of thresholds t_j with p > t_j, thresholds = {-eps, 1/199 .. 198/199, 1+eps}.
 // hist[0][k] counts positives, hist[1][k] negatives; TP_j = sum_{k>j} hist[0][k].
@@ -187,6 +216,14 @@ int launch_dense_opt(float* P, float* s0, float* s1, const float* part, int kspl
 
 int launch_cast_weights(const float* P, __nv_bfloat16* Wb, int n, cudaStream_t stream) {
   cast_weights_kernel<<<std::min(148 * 4, ceil_div(n, 256)), 256, 0, stream>>>(P, Wb, n);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+int launch_table_dense_from(const SparseArgs& a, const OptHyper& h, float* gsum, float inv_n, cudaStream_t stream) {
+  DFM_REQUIRE(gsum != nullptr, "dense_exact on several GPUs: no summed-gradient table");
+  const int grid = int(std::min<long long>(148 * 8, (a.V + 7) / 8));
+  table_dense_from_kernel<<<grid, 256, 0, stream>>>(a, h, gsum, inv_n);
   DFM_LAUNCH_CHECK();
   return DFM_OK;
 }

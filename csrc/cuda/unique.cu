@@ -16,10 +16,10 @@ namespace dfm {
 
 // pos_slot[i] = slot of ids[i]
 __global__ void __launch_bounds__(256)
-unique_lookup_kernel(const int* __restrict__ ids, int n, const int* __restrict__ slot_of,
+unique_lookup_kernel(const int* __restrict__ ids, int n, int V, const int* __restrict__ slot_of,
                      int* __restrict__ pos_slot) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) pos_slot[i] = slot_index(slot_of[__ldg(ids + i)]);
+  if (i < n) pos_slot[i] = slot_index(slot_of[min(max(__ldg(ids + i), 0), V - 1)]);   // same clamp as the claim kernel
 }
 
 // restores the map and publishes the count; one thread per distinct id
@@ -39,8 +39,8 @@ int unique_workspace_init(void* workspace, long long V, cudaStream_t stream) {
 }
 
 // The three launches shared by the caller-workspace and the static-workspace entry points.
-int unique_slots_run(const int* ids, int n, void* workspace, int* uniq_out, int* pos_slot_out, int* count_out,
-                     cudaStream_t stream) {
+int unique_slots_run(const int* ids, int n, long long V, void* workspace, int* uniq_out, int* pos_slot_out,
+                     int* count_out, cudaStream_t stream) {
   int* ws = static_cast<int*>(workspace);
   StepState* st = reinterpret_cast<StepState*>(ws);
   int* slot_of = ws + kUniqueHeaderInts;
@@ -48,8 +48,8 @@ int unique_slots_run(const int* ids, int n, void* workspace, int* uniq_out, int*
   // count = n (one "field" per "example"), n_unique = 0
   if ((rc = launch_set_state(st, n, 0.f, 0, -1, stream))) return rc;
   DFM_CUDA_CHECK(cudaMemsetAsync(&st->n_unique, 0, sizeof(int), stream));
-  if ((rc = launch_dedupe(ids, 1, st, slot_of, uniq_out, n, stream))) return rc;
-  unique_lookup_kernel<<<ceil_div(n, 256), 256, 0, stream>>>(ids, n, slot_of, pos_slot_out);
+  if ((rc = launch_dedupe(ids, 1, st, slot_of, uniq_out, n, 1, n, V, stream))) return rc;
+  unique_lookup_kernel<<<ceil_div(n, 256), 256, 0, stream>>>(ids, n, int(V), slot_of, pos_slot_out);
   DFM_LAUNCH_CHECK();
   unique_reset_kernel<<<std::max(1, std::min(592, ceil_div(n, 256))), 256, 0, stream>>>(st, uniq_out, slot_of, count_out);
   DFM_LAUNCH_CHECK();
@@ -73,5 +73,5 @@ extern "C" int dfm_unique_slots(const int* ids, int n, long long V, void* worksp
                                 int* pos_slot_out, int* count_out, dfm_stream_t stream) {
   DFM_REQUIRE(ids && workspace && uniq_out && pos_slot_out && count_out, "dfm_unique_slots: null argument");
   DFM_REQUIRE(n > 0 && V > 0, "dfm_unique_slots: n and V must be positive (n=%d, V=%lld)", n, V);
-  return unique_slots_run(ids, n, workspace, uniq_out, pos_slot_out, count_out, static_cast<cudaStream_t>(stream));
+  return unique_slots_run(ids, n, V, workspace, uniq_out, pos_slot_out, count_out, static_cast<cudaStream_t>(stream));
 }

@@ -132,13 +132,38 @@ int dfm_engine_buffer(void* engine, const char* name, int index, void** ptr, lon
 int dfm_engine_profile(void* engine, const int* ids, const float* vals, const float* labels, int iters,
                        float* ms_out);
 
-/* Multi-GPU (synchronous data parallel, HVD.py:296) without NCCL on the step path: every rank
- * allocates a symmetric block (comm_alloc, returns a 64-byte CUDA IPC handle), the caller all-gathers
- * the handles, and comm_attach maps the peers.  From then on train_step fuses the dense gradient
- * all-reduce into the optimizer kernel and exchanges the sparse embedding gradients with peer
- * stores over NVLink (csrc/cuda/comm.cu).  All ranks must call train_step the same number of times. */
-int dfm_engine_comm_alloc(void* engine, int world, int rank, void* ipc_handle_out);
-int dfm_engine_comm_attach(void* engine, const void* all_handles);
+/* Multi-GPU (synchronous data parallel, hvd.DistributedOptimizer, HVD.py:296) without NCCL on the step path.
+ * The caller owns the symmetric memory: on every rank it allocates one zero-filled block of
+ * dfm_engine_comm_bytes() bytes, makes every rank's block and every rank's fm_v / fm_w (the tensors given
+ * to dfm_engine_create) addressable from every rank -- CUDA IPC, or cuMem / torch symmetric memory, which
+ * also yields one NVLS multicast address per buffer -- and passes the pointers to comm_attach:
+ *   *_ptrs  `world` device pointers, entry `rank` being this rank's own buffer;
+ *   *_mc    multicast address of the same buffers, or NULL (the kernels then loop over the peers);
+ *   grad_*  only for table_update_mode DENSE_EXACT: zero-filled fp32 tables [feature_size, embedding_size + 8].
+ * From then on train_step runs the dense gradient all-reduce + optimizer as one kernel beside the embedding
+ * backward (multimem.ld_reduce / multimem.st where a multicast address is given) and exchanges the sparse
+ * embedding gradients owner-sharded: row id belongs to rank id % world, which sums the ranks' gradients,
+ * applies the lazy update to its copy of the optimizer slots and stores the new row into every replica
+ * (csrc/cuda/comm.cu).  Optimizer slots of a table row are therefore current on its owner only.
+ * All ranks must call train_step the same number of times; a rank that waits longer than
+ * DFM_COMM_TIMEOUT_S (default 120) seconds for a peer traps.
+ * dfm_engine_comm_multicast: bit 0 = dense all-reduce uses NVLS, bit 1 = table rows are stored through NVLS. */
+int dfm_engine_comm_bytes(void* engine, int world, long long* bytes);
+int dfm_engine_comm_attach(void* engine, int world, int rank, void* const* block_ptrs, void* block_mc,
+                           void* const* fm_v_ptrs, void* fm_v_mc, void* const* fm_w_ptrs, void* fm_w_mc,
+                           void* const* grad_ptrs, void* grad_mc);
+int dfm_engine_comm_multicast(void* engine);
+/* Single-GPU emulation of `n` ranks, for tests and profiling on a one-GPU box: `n` engines created on the
+ * same device act as the ranks.  After emu_attach each engine's train_step stops before the collectives;
+ * once every engine has stepped, emu_collectives launches the two collective kernels ONCE, cooperatively, over
+ * all virtual ranks (separate launches that wait on one another on one GPU are not guaranteed to co-run). */
+int dfm_engine_emu_attach(void* const* engines, int n, void* const* grad_tables);
+int dfm_engine_emu_collectives(void* const* engines, int n, dfm_stream_t stream);
+/* Plain device allocations with CUDA IPC export / import (the fallback symmetric-memory provider). */
+int dfm_dev_alloc(long long bytes, void** ptr);            /* cudaMalloc + zero fill */
+int dfm_dev_free(void* ptr);
+int dfm_ipc_export(const void* ptr, void* handle_out /* 64 bytes */);
+int dfm_ipc_open(const void* handle /* 64 bytes */, void** ptr);
 
 /* ------------------------------------------------------------------------
  * De-duplication of a batch's feature ids (the step that turns B*F row gradients into n_unique
@@ -160,8 +185,11 @@ int dfm_unique_slots(const int* ids, int n, long long V, void* workspace, int* u
  * The scratch is a 4 MiB array compiled into the library and resident on every GPU that loads it,
  * which caps the id space at DFM_UNIQUE_STATIC_MAX_V; a larger V is rejected with an error.
  * The first call on each device looks the array up and fills it with -1 on `stream`: make that call
- * before any stream capture.  All calls on a device share the array: calls issued back to back on
- * one stream are fine, calls that overlap on the GPU race.  Same inputs/outputs as dfm_unique_slots. */
+ * before any stream capture.  That set-up is guarded by a host mutex, and later calls on other streams or
+ * host threads are ordered behind the fill; a call that fails midway makes the next call fill the map again.
+ * All calls on a device share the array: calls issued back to back on one stream are fine, calls whose
+ * kernels overlap on the GPU (different streams with no ordering between them) race on it.
+ * Same inputs/outputs as dfm_unique_slots. */
 #define DFM_UNIQUE_STATIC_MAX_V (1 << 20)
 long long dfm_unique_slots_static_max_v(void);
 int dfm_unique_slots_static(const int* ids, int n, long long V, int* uniq_out, int* pos_slot_out,
