@@ -70,7 +70,21 @@ def sparse_allgather_mean(ids: torch.Tensor, gw: torch.Tensor, gv: torch.Tensor,
 
 
 def attach_fused_collectives(trainer) -> None:
-    """Maps the symmetric gradient buffers of all ranks into this rank and enables the
-    in-kernel NVLink collectives of the fused engine."""
+    """Publishes this rank's symmetric block and embedding tables to every rank and enables the in-kernel NVLink
+    collectives of the fused engine."""
     from .symmetric import attach_engine
-    attach_engine(trainer.engine)
+    attach_engine(trainer.engine, trainer.comm_provider)
+
+
+def gather_owner_sharded_slots(engine) -> None:
+    """Multi-GPU lazy update keeps the optimizer slots of table row ``id`` current on rank ``id % world`` only.
+    Before a checkpoint (or anything else that reads all slots on one rank) every rank fetches the rows it does
+    not own from their owners: one broadcast of a strided slice per owner and slot tensor."""
+    world = dist.get_world_size()
+    if world == 1 or engine.table_update_mode != "lazy":
+        return
+    for t in (engine.fm_w_s0, engine.fm_w_s1, engine.fm_v_s0, engine.fm_v_s1):
+        for owner in range(world):
+            piece = t[owner::world].contiguous()
+            dist.broadcast(piece, src=owner)
+            t[owner::world] = piece

@@ -73,7 +73,9 @@ class FusedEngine:
     def __init__(self, cfg: DeepFMConfig, batch_max: int, optimizer: str = "Adam", lr: float = 5e-4,
                  table_update_mode: str = "lazy", seed: int = 0, device: Optional[torch.device] = None,
                  beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, momentum: float = 0.95,
-                 ftrl_lr_power: float = -0.5, ftrl_l1: float = 0.0, ftrl_l2: float = 0.0):
+                 ftrl_lr_power: float = -0.5, ftrl_l1: float = 0.0, ftrl_l2: float = 0.0, provider=None):
+        """``provider`` (parallel.symmetric): allocates the embedding tables where every rank can address them,
+        which the multi-GPU path needs (the owner of a row stores its new value into every replica)."""
         why = fused_engine_supported(cfg)
         if why:
             raise ValueError(f"fused engine does not cover this configuration: {why}")
@@ -85,6 +87,7 @@ class FusedEngine:
         self.opt_kind = canonical_optimizer(optimizer)
         self.lr = float(lr)
         self.table_update_mode = table_update_mode
+        self.beta1, self.beta2 = float(beta1), float(beta2)
         self._lib = _native.cuda()
         self._type_lib()
 
@@ -104,8 +107,14 @@ class FusedEngine:
         dev, f32 = self.device, torch.float32
         V, Ke = cfg.feature_size, cfg.embedding_size
         i0, i1 = _SLOT_INIT[self.opt_kind]
-        self.fm_w = torch.zeros(V, device=dev, dtype=f32)
-        self.fm_v = torch.zeros(V, Ke, device=dev, dtype=f32)
+        self.world, self.rank = 1, 0
+        self.grad_table = None
+        if provider is not None:
+            self.fm_w = provider.alloc((V,), f32, dev)
+            self.fm_v = provider.alloc((V, Ke), f32, dev)
+        else:
+            self.fm_w = torch.zeros(V, device=dev, dtype=f32)
+            self.fm_v = torch.zeros(V, Ke, device=dev, dtype=f32)
         self.dense = torch.zeros(self.n_dense, device=dev, dtype=f32)
         self.fm_w_s0, self.fm_w_s1 = torch.full_like(self.fm_w, i0), torch.full_like(self.fm_w, i1)
         self.fm_v_s0, self.fm_v_s1 = torch.full_like(self.fm_v, i0), torch.full_like(self.fm_v, i1)
@@ -248,6 +257,13 @@ class FusedEngine:
                 out[f"{k}/{suffix}"] = t
         return out
 
+    def owned_row_mask(self) -> Optional[torch.Tensor]:
+        """Multi-GPU lazy update: bool [V], True where this rank holds the current optimizer slots of the table row
+        (row id belongs to rank id % world; csrc/cuda/comm.cu).  None when every row's slots are local."""
+        if self.world <= 1 or self.table_update_mode != "lazy":
+            return None
+        return (torch.arange(self.cfg.feature_size, device=self.device) % self.world) == self.rank
+
     def sync_weights(self) -> None:
         """Call after writing to ``dense`` from Python (init, restore, broadcast)."""
         _native.check(self._lib.dfm_engine_sync_weights(self._h, self._stream()), "dfm_engine_sync_weights")
@@ -284,7 +300,7 @@ class FusedEngine:
         _native.check(self._lib.dfm_engine_train_step(self._h, ids.data_ptr(), vals.data_ptr(), labels.data_ptr(),
                                                       self._stream()), "dfm_engine_train_step")
 
-    # StepState field order: count, step, lr, loss_sum, n_unique, sparse_done, train, pad
+    # StepState field order: count, step, lr, loss_sum, n_unique, bad_ids, train, pad
     def loss_sum_tensor(self) -> torch.Tensor:
         return self.state_t.view(torch.float32)[3:4]
 
@@ -295,7 +311,7 @@ class FusedEngine:
         s = self.state_t.cpu()
         f = s.view(torch.float32)
         return {"count": int(s[0]), "step": int(s[1]), "lr": float(f[2]), "loss_sum": float(f[3]),
-                "n_unique": int(s[4]), "train": int(s[6])}
+                "n_unique": int(s[4]), "bad_ids": int(s[5]), "train": int(s[6])}
 
     # ------------------------------------------------------------------ graph replay / host pipeline
     def capture(self, count: Optional[int] = None) -> None:
@@ -350,6 +366,51 @@ class FusedEngine:
 
     def launches_per_step(self) -> int:
         return int(self._lib.dfm_engine_launches_per_step(self._h))
+
+
+class EmulatedRanks:
+    """N fused engines on ONE GPU acting as the N ranks of a synchronous data-parallel job.
+
+    Each engine runs its own forward / backward; the two collective kernels (dense all-reduce + optimizer, sparse
+    owner-sharded exchange) are launched once, cooperatively, over all virtual ranks' data
+    (``dfm_engine_emu_collectives``).  This is how the multi-rank protocol of csrc/cuda/comm.cu is tested and
+    profiled on a box with a single GPU; real jobs use one process per GPU (parallel/symmetric.py)."""
+
+    def __init__(self, cfg: DeepFMConfig, n: int, batch_max: int, **engine_kw):
+        from ..parallel.symmetric import LocalProvider
+        self.n = n
+        self.engines = [FusedEngine(cfg, batch_max, provider=LocalProvider(), **engine_kw) for _ in range(n)]
+        lib = self.engines[0]._lib
+        lib.dfm_engine_emu_attach.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        lib.dfm_engine_emu_collectives.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        self._lib = lib
+        self._handles = (C.c_void_p * n)(*[e._h for e in self.engines])
+        grads = None
+        if self.engines[0].table_update_mode == "dense_exact":
+            for e in self.engines:
+                e.grad_table = torch.zeros(cfg.feature_size, cfg.embedding_size + 8, device=e.device)
+            grads = (C.c_void_p * n)(*[C.c_void_p(e.grad_table.data_ptr()) for e in self.engines])
+        _native.check(lib.dfm_engine_emu_attach(self._handles, n, grads), "dfm_engine_emu_attach")
+        for r, e in enumerate(self.engines):
+            e.world, e.rank = n, r
+            e._bufs.clear()
+            e.state_t = e.buffer("state", dtype="i4")
+
+    def load_from_module(self, m: DeepFM) -> None:
+        for e in self.engines:
+            e.load_from_module(m)
+
+    def train_step(self, batches) -> None:
+        """``batches[r] = (ids int32 [B,F], vals, labels)`` of virtual rank r; one synchronous step of all ranks."""
+        for e, (ids, vals, labels) in zip(self.engines, batches):
+            e.train_step(ids, vals, labels)
+        _native.check(self._lib.dfm_engine_emu_collectives(self._handles, self.n, self.engines[0]._stream()),
+                      "dfm_engine_emu_collectives")
+
+    def close(self) -> None:
+        torch.cuda.synchronize()
+        for e in self.engines:
+            e.close()
 
 
 def auc_histogram(prob: torch.Tensor, label: torch.Tensor, hist: torch.Tensor, num_thresholds: int = 200) -> None:

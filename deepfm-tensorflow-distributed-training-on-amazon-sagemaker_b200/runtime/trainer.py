@@ -67,8 +67,13 @@ class Trainer:
         self._loss_ring = None
         if self.backend == "fused":
             from .engine import FusedEngine
+            self.comm_provider = None
+            if self.world > 1:
+                from ..parallel.symmetric import make_provider
+                self.comm_provider = make_provider(self.device)
             self.engine = FusedEngine(cfg, opts.batch_size, optimizer=opts.optimizer, lr=self.lr,
-                                      table_update_mode=opts.table_update_mode, seed=opts.seed, device=self.device)
+                                      table_update_mode=opts.table_update_mode, seed=opts.seed, device=self.device,
+                                      provider=self.comm_provider)
             self.engine.load_from_module(model)
             self.model = None
             self._host_model = model          # kept as a CPU template for export / variable shapes
@@ -84,6 +89,7 @@ class Trainer:
             self._loss_ring = [torch.zeros(1, dtype=torch.float32, pin_memory=pin) for _ in range(2)]
             self._loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
             self._loss_src = [None, None]
+            self._loss_cnt = [opts.batch_size, opts.batch_size]
             self._loss_idx = 0
             self._issued = 0
         else:
@@ -141,14 +147,33 @@ class Trainer:
             d.update(self.optimizer.slots)
         return d
 
+    def prepare_checkpoint(self) -> None:
+        """COLLECTIVE (every rank calls it, before the chief calls :meth:`checkpoint_tensors`): drains the step
+        queue and, on the fused multi-GPU path, brings the optimizer slots of the table rows other ranks own to this
+        rank (the lazy update keeps them current on the owner only, csrc/cuda/comm.cu)."""
+        if self.backend == "fused":
+            torch.cuda.synchronize(self.device)
+            if self.world > 1:
+                from ..parallel.sync_dp import gather_owner_sharded_slots
+                gather_owner_sharded_slots(self.engine)
+                torch.cuda.synchronize(self.device)
+
     def checkpoint_tensors(self) -> Dict[str, np.ndarray]:
         if self.backend == "fused":
             torch.cuda.synchronize(self.device)
         out = {k: v.detach().cpu().numpy().copy() for k, v in self.state_tensors().items()}
         if canonical_optimizer(self.opts.optimizer) == "adam":
-            out["beta1_power"] = np.asarray(0.9 ** (self.global_step + 1), dtype=np.float32)
-            out["beta2_power"] = np.asarray(0.999 ** (self.global_step + 1), dtype=np.float32)
+            # tf.train.AdamOptimizer's non-slot variables: beta^t of the NEXT update (betas are the TF defaults the
+            # engine and the eager optimizer are built with)
+            b1, b2 = self.adam_betas()
+            out["beta1_power"] = np.asarray(b1 ** (self.global_step + 1), dtype=np.float32)
+            out["beta2_power"] = np.asarray(b2 ** (self.global_step + 1), dtype=np.float32)
         return out
+
+    def adam_betas(self) -> Tuple[float, float]:
+        if self.backend == "fused":
+            return float(self.engine.beta1), float(self.engine.beta2)
+        return float(getattr(self.optimizer, "beta1", 0.9)), float(getattr(self.optimizer, "beta2", 0.999))
 
     def load_checkpoint_tensors(self, step: int, tensors: Dict[str, np.ndarray], strict: bool = False) -> List[str]:
         missing = []
@@ -199,7 +224,10 @@ class Trainer:
             vals = hb.feat_vals.to(self.device, non_blocking=True)
             labels = hb.labels.to(self.device, non_blocking=True)
             self.engine.train_step(ids.contiguous(), vals.contiguous(), labels.contiguous())
-            self._after_fused_step()
+            self._after_fused_step(count=hb.count)
+            if self.uses_graph and hb.count != self.opts.batch_size:
+                # the captured graph reads the row count from device state: put the full-batch count back
+                self.engine.set_state(self.opts.batch_size, train=True)
         else:
             self._eager_step(hb.feat_ids.to(self.device), hb.feat_vals.to(self.device), hb.labels.to(self.device))
 
@@ -260,8 +288,9 @@ class Trainer:
                 loader.defer_release = False
                 self.engine.reset_pipeline()
 
-    def _after_fused_step(self, graph_slot: Optional[int] = None) -> None:
+    def _after_fused_step(self, graph_slot: Optional[int] = None, count: Optional[int] = None) -> None:
         i = self._loss_idx
+        self._loss_cnt[i] = self.opts.batch_size if count is None else max(int(count), 1)
         if graph_slot is None:
             self._loss_ring[i].copy_(self.engine.loss_sum_tensor(), non_blocking=True)
         self._loss_src[i] = graph_slot           # None: the trainer's own ring; else: slot of the engine's ring
@@ -317,7 +346,7 @@ class Trainer:
             self._loss_ev[i].synchronize()
             src = self._loss_src[i]
             total = float(self._loss_ring[i][0]) if src is None else float(self._eng_loss[src])
-            return total / self.opts.batch_size
+            return total / self._loss_cnt[i]
         t = self._last_loss_t if wait_current or self._prev_loss_t is None else self._prev_loss_t
         return float(t) if t is not None else float("nan")
 

@@ -112,9 +112,25 @@ def run_eval(trainer: Trainer, flags: Flags, files: Sequence[str], streaming: bo
 
 
 def save(trainer: Trainer, ckpt: CheckpointManager, env: DistEnv) -> None:
+    """COLLECTIVE: every rank drains its queue and waits on the host while the chief writes, so no rank sits inside a
+    collective kernel waiting for a chief that is busy with the file system."""
+    trainer.prepare_checkpoint()
     if env.is_chief and ckpt.model_dir:
         p = ckpt.save(trainer.global_step, trainer.checkpoint_tensors())
         log(env, f"Saving checkpoints for {trainer.global_step} into {p}")
+    barrier()
+
+
+def save_is_due(trainer: Trainer, ckpt: CheckpointManager, env: DistEnv, every: int = 64) -> bool:
+    """The chief's timer decides, for everybody: asked every `every` steps with one tiny broadcast."""
+    if env.world_size <= 1:
+        return ckpt.due()
+    if trainer.global_step % every:
+        return False
+    t = torch.tensor([1 if (env.is_chief and ckpt.due()) else 0], dtype=torch.int32,
+                     device="cuda" if torch.cuda.is_available() else "cpu")
+    dist.broadcast(t, src=0)
+    return bool(t.item())
 
 
 def train_epochs(trainer: Trainer, flags: Flags, env: DistEnv, files: Sequence[str], shard, ckpt: CheckpointManager,
@@ -133,7 +149,7 @@ def train_epochs(trainer: Trainer, flags: Flags, env: DistEnv, files: Sequence[s
                 log(env, f"loss = {trainer.last_loss():.6f}, step = {trainer.global_step} "
                          f"({sps:.1f} global_step/sec, {sps * flags.batch_size * env.world_size:.0f} examples/sec)")
                 t0, s0 = time.time(), trainer.global_step
-            if ckpt.due():
+            if save_is_due(trainer, ckpt, env):
                 save(trainer, ckpt, env)
             if flags.max_steps and trainer.global_step >= flags.max_steps:
                 break

@@ -290,3 +290,23 @@ def test_training_on_the_bundled_data_reaches_the_eager_auc(tmp_path, val_tfreco
     assert aucs["eager"]["auc"] > 0.68 and aucs["fused"]["auc"] > 0.68, aucs
     assert abs(aucs["eager"]["auc"] - aucs["fused"]["auc"]) < 0.02, aucs
     assert abs(aucs["fused"]["auc"] - aucs["fused"]["auc_exact"]) < 0.01, aucs
+
+
+def test_out_of_range_ids_are_clamped_and_counted():
+    """a feature id outside [0, feature_size) must not read or write outside the tables."""
+    cfg, m, eng, ids, vals, labels = _setup(256, [128, 64, 32], V=5000)
+    bad = ids.clone()
+    bad[3, 20], bad[4, 21], bad[5, 22] = -5, 5000, 2 ** 31 - 1
+    eng.train_step(bad.int().contiguous(), vals, labels)
+    torch.cuda.synchronize()
+    st = eng.read_state()
+    assert st["bad_ids"] == 3
+    ref = FusedEngineRef(cfg, m, bad.clamp(0, 4999), vals, labels)
+    assert abs(st["loss_sum"] - ref) < 2e-2 * abs(ref) + 1e-3
+    assert torch.isfinite(eng.variables()["fm_v"]).all()
+    eng.close()
+
+
+def FusedEngineRef(cfg, m, ids, vals, labels):
+    with torch.no_grad():
+        return torch.nn.functional.binary_cross_entropy_with_logits(m(ids, vals), labels, reduction="sum").item()

@@ -85,3 +85,29 @@ def test_static_scratch_variant_rejects_oversized_id_space():
     assert "exceeds the built-in scratch" in msg and str(max_v) in msg
     torch.cuda.synchronize()
     assert int(c.item()) == -7                           # nothing ran
+
+
+def test_out_of_range_ids_stay_inside_the_scratch():
+    """An id outside [0, V) -- a corrupt record, a too-small feature_size -- is treated as the nearest valid id by both
+    entry points, so it can never index outside the id -> slot map (for the built-in scratch that would mean
+    scribbling over whatever the module placed next to the array)."""
+    lib = _lib()
+    V, n = 1000, 4096
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    ids = torch.randint(0, V, (n,), device="cuda", generator=g, dtype=torch.int32)
+    ids[7], ids[8], ids[9] = -3, V, 2 ** 31 - 1
+    clamped = ids.clamp(0, V - 1)
+    ws = torch.empty(lib.dfm_unique_slots_workspace_bytes(V), dtype=torch.uint8, device="cuda")
+    assert lib.dfm_unique_slots_init(ws.data_ptr(), V, stream) == 0
+    u1, p1, c1 = _outputs(n)
+    assert lib.dfm_unique_slots(ids.data_ptr(), n, V, ws.data_ptr(), u1.data_ptr(), p1.data_ptr(), c1.data_ptr(), stream) == 0
+    u2, p2, c2 = _outputs(n)
+    assert lib.dfm_unique_slots_static(ids.data_ptr(), n, V, u2.data_ptr(), p2.data_ptr(), c2.data_ptr(), stream) == 0
+    torch.cuda.synchronize()
+    for u, p, c in ((u1, p1, c1), (u2, p2, c2)):
+        k = int(c.item())
+        assert k == torch.unique(clamped).numel()
+        assert torch.equal(u[p.long()], clamped)
+    # the caller-owned map is back to -1 everywhere: nothing was written past an edge and left behind
+    assert int(ws.view(torch.int32)[128:].max().item()) == -1
