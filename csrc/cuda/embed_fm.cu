@@ -77,7 +77,7 @@ embed_fm_fwd_v4_kernel(const int* __restrict__ ids, const float* __restrict__ va
         if (on) {
           const int raw = __ldg(my_ids + f);
           id[u] = min(max(raw, 0), V - 1);
-          if (raw != id[u]) atomicAdd(&st->bad_ids, 1);
+          if (raw != id[u] && sub == 0) atomicAdd(&st->bad_ids, 1);
         }
         x[u] = on ? __ldg(my_vals + f) : 0.f;
       }

@@ -21,4 +21,5 @@ def test_unique_slots_matches_torch_unique(n, V):
         assert c == ref.numel()
         assert torch.equal(torch.sort(uniq[:c]).values, ref)
         assert torch.equal(uniq[pos.long()], ids)
-    assert int(op.workspace[256:].view(torch.int32).max().item()) == -1
+    hdr = op.workspace.numel() - 4 * V                 # the id -> slot map follows a small header
+    assert int(op.workspace[hdr:].view(torch.int32).max().item()) == -1
