@@ -223,9 +223,9 @@ def main():
         dbg = trainer.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)
         print(f"[rank {rank}] exchange phases us (push, barrier1, index, grid barrier, merge+publish, barrier2): " +
               " ".join(f"{(int(dbg[i]) - int(dbg[0])) / 1e3:.1f}" for i in range(1, 7)) +
-              " | dense (start vs exchange start; local sum+barrier, reduce+publish+barrier, optimizer): " +
+              " | dense (start vs exchange start; local sum, barrier A, reduce+publish, barrier B, optimizer): " +
               f"{(int(dbg[8]) - int(dbg[0])) / 1e3:.1f}; " +
-              " ".join(f"{(int(dbg[i]) - int(dbg[8])) / 1e3:.1f}" for i in range(9, 12)), file=sys.stderr, flush=True)
+              " ".join(f"{(int(dbg[i]) - int(dbg[8])) / 1e3:.1f}" for i in (12, 9, 13, 10, 11)), file=sys.stderr, flush=True)
 
     # ---------------- end to end: pinned host -> device every step, loss back to host ----------------
     for i in range(W):

@@ -186,6 +186,7 @@ dense_sync_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __restric
       *reinterpret_cast<float4*>(my_dP + 4 * size_t(gq)) = acc;
     }
   }
+  stamp(cv, cta, 12);
   cta_signal_all_ranks(cv, cta, 0, epoch);
   cta_wait_all_ranks(cv, cta, 0, epoch);
   stamp(cv, cta, 9);
@@ -210,6 +211,7 @@ dense_sync_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __restric
       }
     }
   }
+  stamp(cv, cta, 13);
   cta_signal_all_ranks(cv, cta, 1, epoch);
   cta_wait_all_ranks(cv, cta, 1, epoch);
   stamp(cv, cta, 10);
@@ -276,22 +278,30 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
   if (threadIdx.x == 0) kstamp_any(a.st, kStampSparse);
 
   // ---------------- phase 0: stream segment o of my records to its owner ----------------
-  for (int oo = 1; oo <= N; ++oo) {
-    const int o = (me + oo) % N;                       // peers first, my own shard last
-    const int n_o = a.st->n_seg[o];
-    const int n_groups = (n_o + G - 1) / G;
-    const int first = (warp_g - ((me + o) % N) * stripe + warps) % warps;
-    float* dst_g = reinterpret_cast<float*>(cv.base[o] + cv.off_in_grads) + size_t(me) * cap * Ke;
-    uint2* dst_t = reinterpret_cast<uint2*>(cv.base[o] + cv.off_in_tails) + size_t(me) * cap;
-    for (int gi0 = first; gi0 < n_groups; gi0 += warps * kRows) {
-      int sidx[kRows], id[kRows];
-      float4 v[kRows];
-      float gw[kRows];
+  // item = (round k, owner) -> one group of G records of that stream; kPush items in flight per warp, so the
+  // dependent loads (id, gradient row) of all owners' groups overlap instead of queueing owner after owner
+  constexpr int kPush = 4;
+  {
+    const int ns_l = lane < N ? a.st->n_seg[lane] : 0;   // my records for owner `lane`
+    int ng_p = (ns_l + G - 1) / G;
 #pragma unroll
-      for (int j = 0; j < kRows; ++j) {
-        sidx[j] = (gi0 + j * warps) * G + g;
-        const bool on = lane_on && sidx[j] < n_o;
-        const size_t slot = size_t(o) * cap + sidx[j];
+    for (int o = 16; o > 0; o >>= 1) ng_p = max(ng_p, __shfl_xor_sync(0xffffffffu, ng_p, o));
+    const int n_pitems = ((ng_p + warps - 1) / warps) * N;
+    for (int it0 = 0; it0 < n_pitems; it0 += kPush) {
+      int sidx[kPush], id[kPush], ow[kPush];
+      float4 v[kPush];
+      float gw[kPush];
+      bool any = false;
+#pragma unroll
+      for (int j = 0; j < kPush; ++j) {
+        const int it = min(it0 + j, n_pitems - 1);
+        const int k = it / N;
+        ow[j] = (me + 1 + (it - k * N)) % N;             // peers first, my own shard last
+        const int n_o = __shfl_sync(0xffffffffu, ns_l, ow[j]);
+        const int first = (warp_g - ((me + ow[j]) % N) * stripe + warps) % warps;
+        sidx[j] = (k * warps + first) * G + g;
+        const bool on = lane_on && it0 + j < n_pitems && sidx[j] < n_o;
+        const size_t slot = size_t(ow[j]) * cap + sidx[j];
         id[j] = on ? a.uniq_ids[slot] : -1;
         v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
         gw[j] = 0.f;
@@ -300,15 +310,20 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
           v[j] = *reinterpret_cast<const float4*>(grow + 4 * sub);
           if (sub == 0) gw[j] = grow[Ke];
         }
+        any |= on;
       }
+      if (!__any_sync(0xffffffffu, any)) continue;
 #pragma unroll
-      for (int j = 0; j < kRows; ++j) {
+      for (int j = 0; j < kPush; ++j) {
         if (id[j] < 0) continue;
+        const int o = ow[j];
         float* grow = a.G + (size_t(o) * cap + sidx[j]) * gp;
+        float* dst_g = reinterpret_cast<float*>(cv.base[o] + cv.off_in_grads) + (size_t(me) * cap + sidx[j]) * Ke;
+        *reinterpret_cast<float4*>(dst_g + 4 * sub) = v[j];
         *reinterpret_cast<float4*>(grow + 4 * sub) = make_float4(0.f, 0.f, 0.f, 0.f);
-        *reinterpret_cast<float4*>(dst_g + size_t(sidx[j]) * Ke + 4 * sub) = v[j];
         if (sub == 0) {
-          dst_t[sidx[j]] = make_uint2(__float_as_uint(gw[j]), uint32_t(id[j]));
+          reinterpret_cast<uint2*>(cv.base[o] + cv.off_in_tails)[size_t(me) * cap + sidx[j]] =
+              make_uint2(__float_as_uint(gw[j]), uint32_t(id[j]));
           grow[Ke] = 0.f;
           a.slot_of[id[j]] = -1;
         }
@@ -339,13 +354,19 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
     const int first = (warp_g - ((r + me) % N) * stripe + warps) % warps;
     return (k * warps + first) * G + g;
   };
-  for (int it = 0; it < n_items; ++it) {
-    int r, nr;
-    const int s = item_record(it, r, nr);
-    if (lane_on && sub == 0 && s < nr) {
-      const int id = int(__ldcg(reinterpret_cast<const unsigned int*>(in_tails + size_t(r) * cap + s) + 1));
-      x.entry_of[size_t(id) - me + r] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(s + 1);
+  for (int it0 = 0; it0 < n_items; it0 += kPush) {     // all ids first, then all entries
+    int id[kPush], rs[kPush], ss[kPush];
+#pragma unroll
+    for (int j = 0; j < kPush; ++j) {
+      int nr;
+      ss[j] = item_record(min(it0 + j, n_items - 1), rs[j], nr);
+      const bool on = lane_on && sub == 0 && it0 + j < n_items && ss[j] < nr;
+      id[j] = on ? int(__ldcg(reinterpret_cast<const unsigned int*>(in_tails + size_t(rs[j]) * cap + ss[j]) + 1)) : -1;
     }
+#pragma unroll
+    for (int j = 0; j < kPush; ++j)
+      if (id[j] >= 0)
+        x.entry_of[size_t(id[j]) - me + rs[j]] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(ss[j] + 1);
   }
   stamp(cv, cta, 3);
   // grid barrier among this rank's CTAs (co-resident)
