@@ -58,6 +58,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--pool", type=int, default=POOL)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the multi-GPU self-check that precedes the timed region")
+    ap.add_argument("--no-pipeline", action="store_true", help="skip the file -> loader -> trainer throughput figure")
     return ap.parse_args()
 
 
@@ -105,13 +107,60 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def nvlink_kib(index: int):
+    """Cumulative NVLink data counters of one GPU (sum over links), KiB: (tx, rx), or None if unavailable."""
+    import re
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(index)], capture_output=True, text=True,
+                             timeout=20).stdout
+    except (OSError, subprocess.TimeoutExpired):
+        return None
+    tx = sum(int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out))
+    rx = sum(int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out))
+    return (tx, rx) if (tx or rx) else None
+
+
+def pool_path(batch: int, pool: int, rank: int) -> str:
+    n = batch * pool
+    return os.path.join(tempfile.gettempdir(), f"dfm_bench_r{rank}_{n}_{FEATURE}.tfrecords")
+
+
+def measure_pipeline(trainer, path: str, batch: int, seconds: float = 2.5):
+    """TFRecord file -> native loader (framing, CRC, Example decode into pinned slabs) -> Trainer.train_batches ->
+    loss on the host: what `python -m deepfm_b200.train` achieves per rank, input pipeline included."""
+    import torch
+    from deepfm_b200.data.loader import BatchLoader
+    workers = max(2, min(32, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
+    loader = BatchLoader([path], FIELD, batch, num_epochs=100000, drop_remainder=True, num_workers=workers, num_slots=8,
+                         ids_dtype=torch.int32, verify_crc=True)
+    n, t0, loss = 0, None, float("nan")
+    gen = trainer.train_batches(loader)
+    try:
+        for _ in gen:
+            if t0 is None:                       # the first batch pays thread start-up; time from the second on
+                torch.cuda.synchronize()
+                t0 = time.time()
+                continue
+            n += 1
+            if n % 64 == 0:
+                loss = trainer.last_loss()
+                if time.time() - t0 >= seconds:
+                    break
+    finally:
+        gen.close()                              # gives the ring slots back before the loader goes away
+        loader.close()
+    torch.cuda.synchronize()
+    dt = time.time() - t0
+    return n * batch / dt, dt, workers, loss
+
+
 def make_host_pool(batch: int, pool: int, rank: int, world: int):
     """Synthetic Criteo-shaped TFRecords -> native loader -> list of pinned batch slabs."""
     import torch
     from deepfm_b200.data.loader import BatchLoader, alloc_slab
     from deepfm_b200.data.tfrecord import generate_synthetic
     n = batch * pool
-    path = os.path.join(tempfile.gettempdir(), f"dfm_bench_r{rank}_{n}_{FEATURE}.tfrecords")
+    path = pool_path(batch, pool, rank)
     if not os.path.exists(path):
         generate_synthetic(path + ".tmp", n, FIELD, FEATURE, n_dense=13, seed=1234 + rank, pos_rate=0.2553, zipf_s=1.05)
         os.replace(path + ".tmp", path)
@@ -161,6 +210,19 @@ def main():
     from deepfm_b200.models.deepfm import DeepFMConfig
     from deepfm_b200.runtime.trainer import Trainer, TrainerOptions
 
+    check = None
+    if world > 1 and args.impl == "fused" and not args.no_check:
+        # correctness of the fused collectives on THIS box, before anything is timed: 4 GD steps on fixed per-rank
+        # batches, fused NVLink kernels vs eager fp32 + NCCL
+        from deepfm_b200.parallel.selfcheck import fused_vs_nccl
+        check = fused_vs_nccl(dev, FIELD, FEATURE, EMB, LAYERS, batch=args.batch)
+        if not (check["replicas_identical"] and check["worst_rel_update_err_vs_nccl"] < 0.05):
+            if rank == 0:
+                print("multi-GPU self-check FAILED: " + json.dumps(check), file=sys.stderr, flush=True)
+            sys.stdout.flush()
+            os.dup2(real_stdout, 1)
+            return 3
+
     cfg = DeepFMConfig(field_size=FIELD, feature_size=FEATURE, embedding_size=EMB, deep_layers=LAYERS,
                        dropout_keep=KEEP, l2_reg=L2)
     opts = TrainerOptions(batch_size=args.batch, optimizer="Adam", learning_rate=LR, table_update_mode="lazy",
@@ -185,6 +247,7 @@ def main():
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
+    nv0 = nvlink_kib(local_rank) if world > 1 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -193,6 +256,7 @@ def main():
     e1.record()
     barrier()
     clocks = sampler.stop()
+    nv1 = nvlink_kib(local_rank) if nv0 else None
     ms_dev = e0.elapsed_time(e1)
     del dev_pool
     if os.environ.get("DFM_BENCH_TIMELINE") and trainer.backend == "fused" and rank == 0:
@@ -207,12 +271,6 @@ def main():
         ph = ["start", "setup", "mma_issued", "staged", "acc_ready", "epilogue", "end"]
         print("embed_bwd CTA(0,0) us: " + "  ".join(f"{ph[i]}@{(int(kd[i]) - int(kd[0])) / 1e3:.1f}" for i in range(7)),
               file=sys.stderr, flush=True)
-        S = 2 * (len(LAYERS) - 1)
-        t1 = int(kd[384])
-        if t1 > 0:
-            print("mid kernel stages (A ready, MMAs issued, acc ready, epilogue done) us: " + " | ".join(
-                " ".join(f"{(int(kd[384 + 4 * s + i]) - t1) / 1e3:.2f}" for i in range(4)) for s in range(S)),
-                file=sys.stderr, flush=True)
         n_cta = 80
         st = [int(kd[8 + 2 * i]) for i in range(n_cta)]
         en = [int(kd[9 + 2 * i]) for i in range(n_cta)]
@@ -245,6 +303,17 @@ def main():
     barrier()
     ms_e2e = h0.elapsed_time(h1)
 
+    # ---------------- input pipeline included: TFRecord file -> loader -> train_batches ----------------
+    pipe = None
+    if not args.no_pipeline:
+        rate, dt, workers, _ = measure_pipeline(trainer, pool_path(args.batch, args.pool, rank), args.batch)
+        pr = torch.tensor([rate], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(pr, op=dist.ReduceOp.MIN)          # the job runs at the pace of its slowest rank
+        pipe = {"value": float(pr.item()) * world, "unit": "examples/s", "seconds": round(dt, 2),
+                "parser_threads_per_rank": workers, "host_cores": os.cpu_count(),
+                "what": "TFRecord file (page cache) -> framing + CRC32C + Example decode -> pinned slabs -> H2D -> step -> loss"}
+
     t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -270,7 +339,17 @@ def main():
         "gpu_launches": trainer.launches_per_step() * K,
         "final_loss": final_loss, "mean_loss": loss_acc / max(K, 1),
         "loader_records_per_sec": parse_rate,
+        "pipeline": pipe,
     }
+    if check is not None:
+        out["replicas_identical"] = check["replicas_identical"]
+        out["worst_rel_update_err_vs_nccl"] = check["worst_rel_update_err_vs_nccl"]
+        out["comm"] = {"provider": check["provider"], "nvls_dense": bool(check["multicast"] & 1),
+                       "nvls_rows": bool(check["multicast"] & 2)}
+    if nv0 and nv1:
+        # measured by the NVLink counters of this rank's GPU around the device-timed region (KiB granularity)
+        out["nvlink_bytes_per_step"] = {"tx": (nv1[0] - nv0[0]) * 1024 / K, "rx": (nv1[1] - nv0[1]) * 1024 / K,
+                                        "rank": rank}
     trainer.close()
     if world > 1:
         dist.destroy_process_group()

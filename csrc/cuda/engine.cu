@@ -77,9 +77,6 @@ struct Engine {
   int emu_ranks = 0;
   unsigned long long* comm_dbg = nullptr;
   unsigned long long* kern_dbg = nullptr;
-  MidParams mid{};               // fused middle of the step (mlp_mid.cu); mid_smem < 0: not usable for this network
-  int mid_smem = -1;
-  bool mid_active = false;       // the current training pass went through the fused middle
   int dedupe_after = 0;          // forward layer after which dedupe is forked (-1: right after embed_fwd); DFM_DEDUPE_AFTER
 
   template <typename T>
@@ -153,15 +150,6 @@ static int engine_build(Engine& E) {
   if ((rc = mlp_layer_set_smem())) return rc;
   if ((rc = embed_bwd_set_smem(c.embedding_size))) return rc;
   if ((rc = wgrad_set_smem())) return rc;
-  {
-    // Opt-in (DFM_MID=1): measured on B200 at batch 2048 the fused middle takes 18.5 us where the five per-layer
-    // launches it replaces take 17.7 us -- one CTA per 128 rows serialises 576 epilogue columns per row on 16 SMs,
-    // which costs more than the four launch latencies it saves (profiles/README.md).
-    const char* v = getenv("DFM_MID");
-    E.mid_smem = (v && v[0] == '1') ? mlp_mid_plan(E.sh, &E.mid) : -1;
-    if (E.mid_smem > 0 && (rc = mlp_mid_set_smem(E.mid_smem))) return rc;
-  }
-
   // ---- TMA descriptors ----
   for (int l = 0; l < sh.L; ++l) {
     const __nv_bfloat16* w = E.Wb + E.off[l];
@@ -245,10 +233,9 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
     DFM_CUDA_CHECK(cudaEventRecord(E.ev_dedupe, E.side));
     return DFM_OK;
   };
-  E.mid_active = train && E.mid_smem > 0;
-  const int dedupe_after = std::min(E.dedupe_after, E.mid_active ? 0 : sh.L - 1);
+  const int dedupe_after = std::min(E.dedupe_after, sh.L - 1);
   if (train && dedupe_after < 0 && (rc = fork_dedupe())) return rc;
-  for (int l = 0; l < (E.mid_active ? 1 : sh.L); ++l) {
+  for (int l = 0; l < sh.L; ++l) {
     LayerParams lp{};
     lp.st = E.st; lp.bias = E.t.dense + E.off[l] + size_t(sh.K[l]) * sh.N[l];
     lp.out = E.act[l + 1]; lp.out_pitch = sh.pitch[l + 1];
@@ -256,18 +243,6 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
     lp.dbg = E.kern_dbg + 384 + 8 * l;            // kern_dbg: [0,328) embed_bwd, [384,480) 8 stamps per layer kernel
     if ((rc = launch_mlp_layer(false, E.fmaps.act[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
     if (train && l == dedupe_after && (rc = fork_dedupe())) return rc;
-  }
-  if (E.mid_active) {
-    // layers 1..L-1 forward, the loss and layers L-1..1 backward in one launch
-    MidParams mp = E.mid;
-    mp.sh = sh; mp.st = E.st;
-    for (int l = 0; l < sh.L; ++l) mp.bias[l] = E.t.dense + E.off[l] + size_t(sh.K[l]) * sh.N[l];
-    for (int l = 0; l <= sh.L; ++l) { mp.act[l] = E.act[l]; mp.dz[l] = E.dz[l]; }
-    mp.w_out = E.t.dense + E.off[sh.L]; mp.fm_part = E.fm_part; mp.labels = labels;
-    mp.logit = E.logit; mp.prob = E.prob; mp.dlogit = E.dlogit;
-    mp.rows_pad = E.Bpad; mp.seed = c.seed;
-    mp.dbg = E.kern_dbg + 384;                    // [384, 384 + 4 * stages)
-    return launch_mlp_mid(E.fmaps, mp, c.batch_max, E.mid_smem, s);
   }
   LossParams q{};
   q.st = E.st; q.h_last = E.act[sh.L]; q.h_pitch = sh.pitch[sh.L]; q.n_last = sh.K[sh.L];
@@ -300,7 +275,7 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   bp.ids = ids; bp.vals = vals; bp.s_sum = E.s_sum; bp.slot_of = E.slot_of; bp.G = E.G; bp.Gw = E.Gw;
   bp.F = c.field_size; bp.Ke = c.embedding_size; bp.V = int(c.feature_size); bp.dbg = E.kern_dbg;
   int rc;
-  for (int l = E.sh.L - 1; l >= 1 && !E.mid_active; --l) {       // dz_{l-1} = (h_l > 0) * (dz_l W_l^T) / keep_{l-1}
+  for (int l = E.sh.L - 1; l >= 1; --l) {       // dz_{l-1} = (h_l > 0) * (dz_l W_l^T) / keep_{l-1}
     LayerParams lp{};
     lp.st = E.st; lp.mask = E.act[l]; lp.mask_pitch = E.sh.pitch[l];
     lp.out = E.dz[l - 1]; lp.out_pitch = E.sh.N[l - 1];
@@ -430,7 +405,7 @@ extern "C" int dfm_engine_launches_per_step(void* h) {
   Engine* E = static_cast<Engine*>(h);
   // dedupe, embed_fwd, L forward layers, loss, L-1 backward layers, embed_bwd, wgrad, dense opt, sparse (1 or 2)
   // single GPU: + dense opt + sparse apply; multi GPU: + one exchange kernel
-  const int mlp = E->mid_smem > 0 ? 2 /* first layer + fused middle */ : E->sh.L + 1 + (E->sh.L - 1);
+  const int mlp = E->sh.L + 1 + (E->sh.L - 1);
   return 2 + mlp + 2 + 2;   // + dense optimizer + sparse apply (multi-GPU: dense all-reduce + sparse exchange)
 }
 

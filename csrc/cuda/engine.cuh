@@ -251,35 +251,6 @@ struct LossParams {
   int rows_pad;
 };
 
-// Fused middle of the step (mlp_mid.cu): forward layers 1..L-1, loss, backward layers L-1..1 in one launch
-constexpr int kMidMaxW = 256;                    // widest layer handled
-constexpr int kMidMaxStages = 2 * (kMaxLayers - 1);
-
-struct MidParams {
-  MlpShape sh;
-  StepState* st;
-  const float* bias[kMaxLayers];          // b_l (fp32)
-  __nv_bfloat16* act[kMaxLayers + 1];     // h_l buffers (row pitch sh.pitch[l])
-  __nv_bfloat16* dz[kMaxLayers + 1];      // dz_l buffers (row pitch N_l; dz_L: 16)
-  const float* w_out;                     // [N_{L-1}] weights then b_out
-  const float* fm_part; const float* labels;
-  float* logit; float* prob; float* dlogit;
-  uint32_t w_off[kMaxLayers];             // byte offset of layer l's weight tiles inside the weight region
-  uint32_t w_bytes;                       // total bytes of the weight region
-  uint32_t a_bytes;                       // bytes of one A-operand buffer: 128 rows x (widest layer rounded up to 64) bf16
-  int rows_pad;
-  unsigned long long seed;
-  unsigned long long* dbg;                // optional per-stage timestamps of CTA 0
-};
-
-__host__ __device__ inline int mid_tiles(int x) { return (x + 63) / 64; }
-
-// Shared memory: [A buffer 0 | A buffer 1 | weight tiles | barriers (256 B) | per-row partial dot products (1 KB) |
-// biases and output weights (8 KB)]
-__host__ __device__ inline uint32_t mid_smem_bytes(uint32_t a_bytes, uint32_t w_bytes) {
-  return 2u * a_bytes + w_bytes + 256u + 1024u + 8192u + 1024u;
-}
-
 // Multi-GPU view: every rank's symmetric block and embedding tables are addressable from every rank (peer mappings over
 // NVLink; optionally also through one NVLS multicast address that stores to / reduces over all of them).
 // Identical on all ranks except `rank`.
@@ -340,9 +311,6 @@ int embed_bwd_set_smem(int);
 int launch_embed_bwd(const FwdMaps&, const BwdParams&, int, cudaStream_t);
 int wgrad_set_smem();
 int launch_wgrad(const WgradMaps&, const WgradParams&, int, cudaStream_t);
-int mlp_mid_plan(const MlpShape&, MidParams*);
-int mlp_mid_set_smem(int);
-int launch_mlp_mid(const FwdMaps&, const MidParams&, int, int, cudaStream_t);
 int launch_set_state(StepState*, int, float, int, int, cudaStream_t);
 int launch_dense_opt(float*, float*, float*, const float*, int, size_t, __nv_bfloat16*, int, const StepState*,
                      const OptHyper&, float, int wb_skip_lo, int wb_skip_hi, cudaStream_t);

@@ -30,20 +30,6 @@ const char* dfm_last_error(void);
 int dfm_version(void);
 
 /* ------------------------------------------------------------------------
- * Generic bf16 GEMM on tcgen05/TMEM fed by TMA (building block + unit-test
- * surface for the fused MLP kernels).
- *   C[M,N] (fp32, row-major, leading dim ldc) = A[M,K] * B[N,K]^T (+ bias[N]) (relu)
- * A and B are bf16, K contiguous ("K-major"); lda/ldb in elements, multiples of 8.
- * b_mn_major != 0: B is given as [K,N] with N contiguous (ldb = its leading dim).
- * a_mn_major != 0: A is given as [K,M] with M contiguous.
- * Replaces the cuBLAS SGEMM behind tf.contrib.layers.fully_connected, HVD.py:224.
- * ---------------------------------------------------------------------- */
-int dfm_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major,
-                  float* C, int ldc, int M, int N, int K, const float* bias, int relu,
-                  dfm_stream_t stream);
-
-
-/* ------------------------------------------------------------------------
  * Optimizers (tf.train.*Optimizer of HVD.py:281-294) and table update modes
  * ---------------------------------------------------------------------- */
 #define DFM_OPT_ADAM 0

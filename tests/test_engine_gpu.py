@@ -193,34 +193,6 @@ def test_pipelined_graph_step_matches_plain_launches():
     a.close(); b.close()
 
 
-def test_fused_middle_matches_per_layer_kernels(monkeypatch):
-    """DFM_MID=1 (layers 1..L-1 forward, loss, layers L-1..1 backward in one launch) == the per-layer kernels."""
-    outs = []
-    for mid in ("0", "1"):
-        monkeypatch.setenv("DFM_MID", mid)
-        cfg, m, eng, ids, vals, labels = _setup(300, [256, 128, 64], keep=[0.5, 0.8, 0.5], opt="GD", lr=0.0)
-        eng.train_step(ids.int().contiguous(), vals, labels)
-        torch.cuda.synchronize()
-        got = {f"act{l}": eng.buffer("act", l, "bf16").clone() for l in (2, 3)}
-        got.update({f"dz{l}": eng.buffer("dz", l, "bf16").clone() for l in (0, 1, 2, 3)})
-        got["prob"] = eng.buffer("prob").clone()[:300]
-        got["dlogit"] = eng.buffer("dlogit").clone()[:300]
-        got["launches"] = eng.launches_per_step()
-        outs.append(got)
-        eng.close()
-    assert outs[0]["launches"] == 12 and outs[1]["launches"] == 8
-    # the output layer's dot product is summed in a different order (halves vs quarters of a row), and one wide
-    # MMA replaces four 64-column tiles: equal up to rounding
-    torch.testing.assert_close(outs[0]["prob"], outs[1]["prob"], rtol=1e-3, atol=1e-30)
-    for k in ("dlogit", "dz3", "dz2", "dz1", "dz0"):
-        a, b = outs[0][k].float(), outs[1][k].float()
-        assert (a - b).abs().max().item() <= 2e-2 * a.abs().max().item() + 1e-12, k
-        assert ((a != 0) == (b != 0)).float().mean().item() > 0.999, k
-    for k, width in (("act2", 128), ("act3", 64)):                    # rows past the batch are never written
-        pitch = (width + 1 + 15) // 16 * 16
-        assert torch.equal(outs[0][k].view(-1, pitch)[:300, :width], outs[1][k].view(-1, pitch)[:300, :width]), k
-
-
 def test_train_batches_pipelines_the_loader(tmp_path):
     """Trainer.train_batches (look-ahead + in-graph prefetch + deferred slot release) == one batch at a time."""
     from deepfm_b200.data.loader import BatchLoader
