@@ -83,6 +83,23 @@ __host__ __device__ inline void philox4x32(uint32_t seed_lo, uint32_t seed_hi, u
   out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
 }
 
+// Dropout keep decisions of 8 consecutive activation columns [8*colgroup, 8*colgroup+8) of example `row` after
+// hidden layer `layer` at optimizer step `step`: bit i set = column 8*colgroup+i is kept (probability `keep`).
+// One Philox call yields eight 16-bit uniforms.  Every kernel that needs a mask recomputes it from here.
+__host__ __device__ inline uint32_t dropout_keep_bits8(unsigned long long seed, uint32_t row, uint32_t layer,
+                                                       uint32_t colgroup, uint32_t step, float keep) {
+  const uint32_t thr = uint32_t(keep * 65536.f);
+  uint32_t rnd[4];
+  philox4x32(uint32_t(seed), uint32_t(seed >> 32), row, layer, colgroup, step, rnd);
+  uint32_t bits = 0u;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    bits |= ((rnd[i] & 0xffffu) < thr ? 1u : 0u) << (2 * i);
+    bits |= ((rnd[i] >> 16) < thr ? 1u : 0u) << (2 * i + 1);
+  }
+  return bits;
+}
+
 // uniform in [0,1)
 __host__ __device__ inline float u32_to_unit(uint32_t x) { return (x >> 8) * (1.0f / 16777216.0f); }
 

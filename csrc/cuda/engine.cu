@@ -33,6 +33,13 @@ struct Engine {
   float* dP = nullptr;
   __nv_bfloat16* act[kMaxLayers + 1] = {};
   __nv_bfloat16* dz[kMaxLayers + 1] = {};
+  // batch norm (cfg.batch_norm): a_l = relu(.) before normalisation, per-batch {mean, rstd}, offsets of
+  // {gamma, beta} inside the flat dense vector and of {moving mean, moving variance} inside t.bn_moving
+  bool bn = false;
+  __nv_bfloat16* pre[kMaxLayers] = {};
+  float* bn_save[kMaxLayers] = {};
+  size_t off_bn[kMaxLayers] = {};
+  size_t off_mov[kMaxLayers] = {};
   float *s_sum = nullptr, *fm_part = nullptr, *logit = nullptr, *prob = nullptr, *dlogit = nullptr;
   float *G = nullptr, *Gw = nullptr;
   int *slot_of = nullptr, *uniq_ids = nullptr;
@@ -111,11 +118,21 @@ static int engine_build(Engine& E) {
   for (int l = 0; l <= sh.L; ++l) sh.pitch[l] = round_up(sh.K[l] + 1, 16);   // rows start on 32-byte boundaries (256-bit stores)
   E.Bpad = round_up(c.batch_max, kTileM);
 
-  size_t o = 0;
-  for (int l = 0; l <= sh.L; ++l) {
+  E.bn = c.batch_norm != 0;
+  DFM_REQUIRE(!E.bn || E.t.bn_moving, "batch_norm needs the bn_moving tensor");
+  DFM_REQUIRE(c.loss_type == DFM_LOSS_LOG || c.loss_type == DFM_LOSS_SQUARE, "unknown loss_type %d", c.loss_type);
+  size_t o = 0, om = 0;
+  for (int l = 0; l < sh.L; ++l) {
     E.off[l] = o;
     o += size_t(sh.K[l] + 1) * sh.N[l];
   }
+  if (E.bn)
+    for (int l = 0; l < sh.L; ++l) {     // [gamma | beta] per layer, between the hidden layers and the out layer
+      E.off_bn[l] = o;   o += 2 * size_t(sh.N[l]);
+      E.off_mov[l] = om; om += 2 * size_t(sh.N[l]);
+    }
+  E.off[sh.L] = o;
+  o += size_t(sh.K[sh.L] + 1) * sh.N[sh.L];
   E.off[sh.L + 1] = o;       // fm_bias
   E.n_dense = int(o + 1);
 
@@ -133,6 +150,11 @@ static int engine_build(Engine& E) {
     const int ncol = l < sh.L ? sh.N[l] : 16;
     if ((rc = E.alloc(&E.dz[l], rows * ncol))) return rc;
   }
+  if (E.bn)
+    for (int l = 0; l < sh.L; ++l) {
+      if ((rc = E.alloc(&E.pre[l], rows * sh.N[l]))) return rc;
+      if ((rc = E.alloc(&E.bn_save[l], 2 * size_t(sh.N[l])))) return rc;
+    }
   if ((rc = E.alloc(&E.s_sum, rows * c.embedding_size))) return rc;
   if ((rc = E.alloc(&E.fm_part, rows))) return rc;
   if ((rc = E.alloc(&E.logit, rows))) return rc;
@@ -209,6 +231,17 @@ static int engine_build(Engine& E) {
   return DFM_OK;
 }
 
+static BnParams bn_params(const Engine& E, int l) {
+  BnParams b{};
+  b.st = E.st; b.pre = E.pre[l]; b.out = E.act[l + 1]; b.dy = E.dz[l];
+  b.gamma = E.t.dense + E.off_bn[l]; b.beta = b.gamma + E.sh.N[l];
+  b.moving = E.t.bn_moving + E.off_mov[l]; b.save = E.bn_save[l];
+  b.dgamma = E.dP + E.off_bn[l];                 // slice 0 of the split-K gradient buffer; the other slices stay zero
+  b.n = E.sh.N[l]; b.out_pitch = E.sh.pitch[l + 1]; b.layer = l;
+  b.keep = E.sh.keep[l]; b.decay = E.cfg.bn_decay; b.eps = E.cfg.bn_eps; b.seed = E.cfg.seed;
+  return b;
+}
+
 static int engine_forward(Engine& E, const int* ids, const float* vals, const float* labels, int train,
                           cudaStream_t s) {
   const dfm_engine_config& c = E.cfg;
@@ -240,8 +273,10 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
     lp.st = E.st; lp.bias = E.t.dense + E.off[l] + size_t(sh.K[l]) * sh.N[l];
     lp.out = E.act[l + 1]; lp.out_pitch = sh.pitch[l + 1];
     lp.n_out = sh.N[l]; lp.k_red = sh.K[l]; lp.b_box_rows = 64; lp.layer = l; lp.keep = sh.keep[l]; lp.seed = c.seed;
+    if (E.bn) { lp.out = E.pre[l]; lp.out_pitch = sh.N[l]; lp.keep = 1.f; }   // BN kernel normalises and drops out
     lp.dbg = E.kern_dbg + 384 + 8 * l;            // kern_dbg: [0,328) embed_bwd, [384,480) 8 stamps per layer kernel
     if ((rc = launch_mlp_layer(false, E.fmaps.act[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
+    if (E.bn && (rc = launch_bn_fwd(bn_params(E, l), s))) return rc;
     if (train && l == dedupe_after && (rc = fork_dedupe())) return rc;
   }
   LossParams q{};
@@ -250,6 +285,7 @@ static int engine_forward(Engine& E, const int* ids, const float* vals, const fl
   q.logit = E.logit; q.prob = E.prob; q.dlogit = train ? E.dlogit : nullptr;
   q.dz_last = train ? E.dz[sh.L - 1] : nullptr; q.dz_out = E.dz[sh.L];
   q.keep_last = sh.keep[sh.L - 1]; q.rows_pad = E.Bpad;
+  q.loss_type = c.loss_type; q.bn = E.bn; q.seed = c.seed; q.last_layer = sh.L - 1;
   return launch_loss_init(q, train ? E.Bpad : c.batch_max, s);
 }
 
@@ -275,14 +311,18 @@ static int engine_backward_update(Engine& E, const int* ids, const float* vals, 
   bp.ids = ids; bp.vals = vals; bp.s_sum = E.s_sum; bp.slot_of = E.slot_of; bp.G = E.G; bp.Gw = E.Gw;
   bp.F = c.field_size; bp.Ke = c.embedding_size; bp.V = int(c.feature_size); bp.dbg = E.kern_dbg;
   int rc;
+  // batch norm: the loss kernel / each backward layer kernel leaves the gradient w.r.t. the BN OUTPUT in dz[l];
+  // bn_bwd turns it into the gradient w.r.t. the layer's pre-activation, in place, and writes dgamma / dbeta
+  if (E.bn && (rc = launch_bn_bwd(bn_params(E, E.sh.L - 1), E.Bpad, s))) return rc;
   for (int l = E.sh.L - 1; l >= 1; --l) {       // dz_{l-1} = (h_l > 0) * (dz_l W_l^T) / keep_{l-1}
     LayerParams lp{};
     lp.st = E.st; lp.mask = E.act[l]; lp.mask_pitch = E.sh.pitch[l];
     lp.out = E.dz[l - 1]; lp.out_pitch = E.sh.N[l - 1];
     lp.n_out = E.sh.K[l]; lp.k_red = E.sh.N[l]; lp.b_box_rows = 64; lp.layer = l; lp.keep = E.sh.keep[l - 1];
-    lp.seed = c.seed;
+    lp.seed = c.seed; lp.bn = E.bn;
     lp.dbg = E.kern_dbg + 384 + 8 * (kMaxLayers + l);
     if ((rc = launch_mlp_layer(true, E.fmaps.dz[l], E.fmaps.w[l], lp, c.batch_max, s))) return rc;
+    if (E.bn && (rc = launch_bn_bwd(bn_params(E, l - 1), E.Bpad, s))) return rc;
   }
 
   // fork: the embedding gradient and the sparse update stay on the main stream (they are the critical path, and a
@@ -406,7 +446,7 @@ extern "C" int dfm_engine_launches_per_step(void* h) {
   // dedupe, embed_fwd, L forward layers, loss, L-1 backward layers, embed_bwd, wgrad, dense opt, sparse (1 or 2)
   // single GPU: + dense opt + sparse apply; multi GPU: + one exchange kernel
   const int mlp = E->sh.L + 1 + (E->sh.L - 1);
-  return 2 + mlp + 2 + 2;   // + dense optimizer + sparse apply (multi-GPU: dense all-reduce + sparse exchange)
+  return 2 + mlp + 2 + 2 + (E->bn ? 2 * E->sh.L : 0);   // + dense optimizer + sparse apply (multi-GPU: dense all-reduce + sparse exchange)
 }
 
 // ---- phase timing (warm, CUDA events) ----------------------------------------------------------
@@ -837,6 +877,17 @@ extern "C" int dfm_engine_buffer(void* h, const char* name, int index, void** pt
   }
   *ptr = p;
   *n_elems = n;
+  return DFM_OK;
+}
+
+// offsets of [gamma | beta] of layer l inside the dense vector and of [moving_mean | moving_variance] inside bn_moving
+extern "C" int dfm_engine_bn_layout(void* h, long long* dense_offsets, long long* moving_offsets) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(E->bn, "dfm_engine_bn_layout: the engine was created without batch_norm");
+  for (int l = 0; l < E->sh.L; ++l) {
+    dense_offsets[l] = (long long)E->off_bn[l];
+    moving_offsets[l] = (long long)E->off_mov[l];
+  }
   return DFM_OK;
 }
 

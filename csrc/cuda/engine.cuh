@@ -236,11 +236,33 @@ struct LayerParams {
   int layer;
   float keep;                     // forward: keep_l ; backward: keep_{l-1}
   unsigned long long seed;
+  int bn;                         // backward with batch norm: the output is masked by the dropout bits of layer-1 only
+                                  // (recomputed), the ReLU / BN part of the chain is bn_bwd's
   unsigned long long* dbg;        // optional: 8 phase timestamps of CTA (0,0)
 };
 
+// Batch normalisation after the ReLU of a hidden layer (HVD.py:230-233,306-328), one launch per layer and direction.
+struct BnParams {
+  StepState* st;
+  const __nv_bfloat16* pre;       // a = relu(h W + b)  [rows, n], row pitch n
+  __nv_bfloat16* out;             // forward: dropout(BN(a)), row pitch out_pitch
+  __nv_bfloat16* dy;              // backward: in: gradient w.r.t. BN output (dropout already applied); out: dz of the layer
+  const float* gamma; const float* beta;
+  float* moving;                  // [mean n | variance n]
+  float* save;                    // [mean n | rstd n] of the current batch (forward writes, backward reads)
+  float* dgamma;                  // backward: [dgamma n | dbeta n] inside slice 0 of the dense gradient buffer
+  int n, out_pitch, layer;
+  float keep, decay, eps;
+  unsigned long long seed;
+};
+int launch_bn_fwd(const BnParams&, cudaStream_t);
+int launch_bn_bwd(const BnParams&, int rows_pad, cudaStream_t);
+
 struct LossParams {
   StepState* st;
+  int loss_type;                  // DFM_LOSS_*
+  int bn;                         // batch-norm tower: dz_last is the gradient w.r.t. the BN output (no ReLU mask here)
+  unsigned long long seed; int last_layer;   // dropout stream of the last hidden layer (bn: keep bits are recomputed)
   const __nv_bfloat16* h_last; int h_pitch; int n_last;
   const float* w_out;             // P_out: [n_last] weights then b_out
   const float* fm_part; const float* labels;

@@ -135,7 +135,7 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
       for (int i = 0; i < kLayerN / 8; ++i) {
         hmask[i] = make_uint4(0u, 0u, 0u, 0u);
-        if (valid && 8 * i < n_here) hmask[i] = __ldg(reinterpret_cast<const uint4*>(mask_row) + i);
+        if (valid && !p.bn && 8 * i < n_here) hmask[i] = __ldg(reinterpret_cast<const uint4*>(mask_row) + i);
       }
     }
 
@@ -143,19 +143,21 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // uniforms, so a row's 64 keep bits cost eight calls, all hidden behind the MMA main loop.
     uint32_t keep_bits[kLayerN / 32] = {0u, 0u};
     if (!kBackward && drop) {
-      const uint32_t thr = uint32_t(p.keep * 65536.f);
 #pragma unroll
       for (int g = 0; g < kLayerN / 8; ++g) {
         if (8 * g >= n_here) break;
-        uint32_t rnd[4];
-        philox4x32(uint32_t(p.seed), uint32_t(p.seed >> 32), uint32_t(b), uint32_t(p.layer),
-                   uint32_t((n0 >> 3) + g), step, rnd);
-        uint32_t bits = 0u;
+        const uint32_t bits = dropout_keep_bits8(p.seed, uint32_t(b), uint32_t(p.layer), uint32_t((n0 >> 3) + g), step, p.keep);
+        keep_bits[g >> 2] |= bits << (8 * (g & 3));
+      }
+    }
+    if (kBackward && p.bn) {
+      // batch-norm tower: the output is the gradient w.r.t. the BN output of layer-1, i.e. only that layer's dropout
+      // applies here (bits recomputed); bn_bwd finishes the chain through BN and the ReLU
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          bits |= ((rnd[i] & 0xffffu) < thr ? 1u : 0u) << (2 * i);
-          bits |= ((rnd[i] >> 16) < thr ? 1u : 0u) << (2 * i + 1);
-        }
+      for (int g = 0; g < kLayerN / 8; ++g) {
+        if (8 * g >= n_here) break;
+        const uint32_t bits = drop ? dropout_keep_bits8(p.seed, uint32_t(b), uint32_t(p.layer - 1), uint32_t((n0 >> 3) + g), step, p.keep)
+                                   : 0xffu;
         keep_bits[g >> 2] |= bits << (8 * (g & 3));
       }
     }
@@ -179,13 +181,19 @@ mlp_layer_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int i = 0; i < 16; ++i) a[i] = ((kb >> i) & 1u) ? a[i] * inv_keep : 0.f;
         }
       } else {
-        const uint4 h0 = hmask[c0 / 8], h1 = hmask[c0 / 8 + 1];
-        const uint32_t hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+        if (p.bn) {
+          const uint32_t kb = keep_bits[c0 >> 5] >> (c0 & 31);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&hv[i]);
-          a[2 * i] = __low2float(v) > 0.f ? __uint_as_float(r[2 * i]) * inv_keep : 0.f;
-          a[2 * i + 1] = __high2float(v) > 0.f ? __uint_as_float(r[2 * i + 1]) * inv_keep : 0.f;
+          for (int i = 0; i < 16; ++i) a[i] = ((kb >> i) & 1u) ? __uint_as_float(r[i]) * inv_keep : 0.f;
+        } else {
+          const uint4 h0 = hmask[c0 / 8], h1 = hmask[c0 / 8 + 1];
+          const uint32_t hv[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&hv[i]);
+            a[2 * i] = __low2float(v) > 0.f ? __uint_as_float(r[2 * i]) * inv_keep : 0.f;
+            a[2 * i + 1] = __high2float(v) > 0.f ? __uint_as_float(r[2 * i + 1]) * inv_keep : 0.f;
+          }
         }
       }
       // rows past the batch: forward leaves them untouched, backward must write zeros (they are
@@ -249,8 +257,13 @@ loss_init_kernel(const LossParams p) {
     const float pr = 1.f / (1.f + __expf(-z));
     if (p.labels) {
       const float y = __ldg(p.labels + b);
-      if (part == 0) loss = fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
-      dl = (pr - y) / float(count);
+      if (p.loss_type == DFM_LOSS_SQUARE) {            // mean (sigmoid(y) - label)^2
+        if (part == 0) loss = (pr - y) * (pr - y);
+        dl = 2.f * (pr - y) * pr * (1.f - pr) / float(count);
+      } else {
+        if (part == 0) loss = fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
+        dl = (pr - y) / float(count);
+      }
     }
     if (part == 0) {
       p.logit[b] = z;
@@ -265,14 +278,19 @@ loss_init_kernel(const LossParams p) {
     __nv_bfloat16* dz = p.dz_last + size_t(b) * p.n_last;
     for (int c = part * 8; c < p.n_last; c += 8 * LPE) {
       uint4 hv = make_uint4(0u, 0u, 0u, 0u);
-      if (valid) hv = __ldg(reinterpret_cast<const uint4*>(h + c));
+      if (valid && !p.bn) hv = __ldg(reinterpret_cast<const uint4*>(h + c));
       const uint32_t w4[4] = {hv.x, hv.y, hv.z, hv.w};
+      // batch-norm tower: h_L = dropout(BN(a)) can be <= 0 where it was kept, so the keep bits are recomputed
+      const uint32_t kb = !p.bn ? 0u : drop ? dropout_keep_bits8(p.seed, uint32_t(b), uint32_t(p.last_layer), uint32_t(c >> 3),
+                                                                uint32_t(p.st->step), p.keep_last) : 0xffu;
       uint32_t o[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&w4[i]);
-        const float d0 = (c + 2 * i < p.n_last && __low2float(v) > 0.f) ? dl * __ldg(p.w_out + c + 2 * i) * scale : 0.f;
-        const float d1 = (c + 2 * i + 1 < p.n_last && __high2float(v) > 0.f) ? dl * __ldg(p.w_out + c + 2 * i + 1) * scale : 0.f;
+        const bool on0 = p.bn ? ((kb >> (2 * i)) & 1u) != 0 : __low2float(v) > 0.f;
+        const bool on1 = p.bn ? ((kb >> (2 * i + 1)) & 1u) != 0 : __high2float(v) > 0.f;
+        const float d0 = (valid && c + 2 * i < p.n_last && on0) ? dl * __ldg(p.w_out + c + 2 * i) * scale : 0.f;
+        const float d1 = (valid && c + 2 * i + 1 < p.n_last && on1) ? dl * __ldg(p.w_out + c + 2 * i + 1) * scale : 0.f;
         o[i] = pack_bf16x2(d0, d1);
       }
       *reinterpret_cast<uint4*>(dz + c) = make_uint4(o[0], o[1], o[2], o[3]);

@@ -35,12 +35,13 @@ class _EngineConfig(C.Structure):
         ("lr", C.c_float), ("l2_reg", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
         ("momentum", C.c_float), ("ftrl_lr_power", C.c_float), ("ftrl_l1", C.c_float), ("ftrl_l2", C.c_float),
         ("seed", C.c_uint64),
+        ("batch_norm", C.c_int32), ("loss_type", C.c_int32), ("bn_decay", C.c_float), ("bn_eps", C.c_float),
     ]
 
 
 class _EngineTensors(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
-        "fm_w", "fm_w_s0", "fm_w_s1", "fm_v", "fm_v_s0", "fm_v_s1", "dense", "dense_s0", "dense_s1")]
+        "fm_w", "fm_w_s0", "fm_w_s1", "fm_v", "fm_v_s0", "fm_v_s1", "dense", "dense_s0", "dense_s1", "bn_moving")]
 
 
 class _DevMem:
@@ -56,10 +57,6 @@ def _round_up(a: int, b: int) -> int:
 
 def fused_engine_supported(cfg: DeepFMConfig) -> Optional[str]:
     """None if the fused kernels cover this configuration, else the reason they do not."""
-    if cfg.batch_norm:
-        return "batch_norm needs batch-wide statistics between layers; it runs on the layered path"
-    if cfg.loss_type != "log_loss":
-        return "the fused loss epilogue implements log_loss only"
     if cfg.embedding_size % 16 or cfg.embedding_size > 64:
         return "embedding_size must be a multiple of 16 and <= 64"
     if not 1 <= len(cfg.deep_layers) <= MAX_LAYERS:
@@ -96,11 +93,20 @@ class FusedEngine:
         self.Np = [_round_up(n, 16) for n in cfg.deep_layers]           # padded widths
         self.K = [cfg.field_size * cfg.embedding_size] + self.Np        # K[l] input width of layer l
         self.N = self.Np + [1]
-        self.off = []
-        o = 0
-        for l in range(L + 1):
+        # flat dense vector: [P_0 | .. | P_{L-1} | (batch norm: [gamma_l | beta_l] per layer) | P_out | fm_bias]
+        self.off, self.off_bn, self.off_mov = [], [], []
+        o = om = 0
+        for l in range(L):
             self.off.append(o)
             o += (self.K[l] + 1) * self.N[l]
+        if cfg.batch_norm:
+            for l in range(L):
+                self.off_bn.append(o)
+                o += 2 * self.N[l]
+                self.off_mov.append(om)
+                om += 2 * self.N[l]
+        self.off.append(o)            # P_out
+        o += (self.K[L] + 1) * self.N[L]
         self.off.append(o)            # fm_bias
         self.n_dense = o + 1
 
@@ -119,6 +125,12 @@ class FusedEngine:
         self.fm_w_s0, self.fm_w_s1 = torch.full_like(self.fm_w, i0), torch.full_like(self.fm_w, i1)
         self.fm_v_s0, self.fm_v_s1 = torch.full_like(self.fm_v, i0), torch.full_like(self.fm_v, i1)
         self.dense_s0, self.dense_s1 = torch.full_like(self.dense, i0), torch.full_like(self.dense, i1)
+        self.bn_moving = None
+        if cfg.batch_norm:
+            self.bn_moving = torch.zeros(max(om, 1), device=dev, dtype=f32)
+            for l in range(L):        # gamma = 1, moving variance = 1 (padding units included: they only ever see zeros)
+                self.dense[self.off_bn[l]:self.off_bn[l] + self.N[l]] = 1.0
+                self.bn_moving[self.off_mov[l] + self.N[l]:self.off_mov[l] + 2 * self.N[l]] = 1.0
 
         ec = _EngineConfig()
         ec.batch_max, ec.field_size, ec.embedding_size, ec.n_layers = self.batch_max, cfg.field_size, Ke, L
@@ -132,9 +144,14 @@ class FusedEngine:
         ec.beta1, ec.beta2, ec.eps, ec.momentum = beta1, beta2, eps, momentum
         ec.ftrl_lr_power, ec.ftrl_l1, ec.ftrl_l2 = ftrl_lr_power, ftrl_l1, ftrl_l2
         ec.seed = seed & 0xFFFFFFFFFFFFFFFF
-        et = _EngineTensors(*[t.data_ptr() for t in (
+        ec.batch_norm = int(bool(cfg.batch_norm))
+        ec.loss_type = {"log_loss": 0, "square_loss": 1}[cfg.loss_type]
+        ec.bn_decay = float(cfg.batch_norm_decay)
+        from ..models.deepfm import BN_EPS
+        ec.bn_eps = BN_EPS
+        et = _EngineTensors(*([t.data_ptr() for t in (
             self.fm_w, self.fm_w_s0, self.fm_w_s1, self.fm_v, self.fm_v_s0, self.fm_v_s1,
-            self.dense, self.dense_s0, self.dense_s1)])
+            self.dense, self.dense_s0, self.dense_s1)] + [self.bn_moving.data_ptr() if cfg.batch_norm else None]))
         h = C.c_void_p()
         with torch.cuda.device(self.device):
             _native.check(self._lib.dfm_engine_create(C.byref(ec), C.byref(et), C.byref(h)), "dfm_engine_create")
@@ -212,6 +229,12 @@ class FusedEngine:
             n = cfg.deep_layers[l]
             w[:k_prev, :n] = m.mlp_w[l].detach()
             b[:n] = m.mlp_b[l].detach()
+            if cfg.batch_norm:
+                ob, om, N = self.off_bn[l], self.off_mov[l], self.N[l]
+                self.dense[ob:ob + n] = m.bn_gamma[l].detach()
+                self.dense[ob + N:ob + N + n] = m.bn_beta[l].detach()
+                self.bn_moving[om:om + n] = getattr(m, f"bn_mean_{l}")
+                self.bn_moving[om + N:om + N + n] = getattr(m, f"bn_var_{l}")
             k_prev = n
         w, b = self._layer_views(self.dense, self.L)
         w[:k_prev, :] = m.out_w.detach()
@@ -225,9 +248,9 @@ class FusedEngine:
 
     def variables(self) -> "OrderedDict[str, torch.Tensor]":
         """TF-named parameter tensors (unpadded views / slices of the engine's storage)."""
-        return self._named(self.fm_w, self.fm_v, self.dense)
+        return self._named(self.fm_w, self.fm_v, self.dense, self.bn_moving)
 
-    def _named(self, fm_w, fm_v, dense) -> "OrderedDict[str, torch.Tensor]":
+    def _named(self, fm_w, fm_v, dense, moving=None) -> "OrderedDict[str, torch.Tensor]":
         cfg = self.cfg
         d: "OrderedDict[str, torch.Tensor]" = OrderedDict()
         d["fm_bias"] = dense[self.off[self.L + 1]:self.off[self.L + 1] + 1]
@@ -239,6 +262,14 @@ class FusedEngine:
             n = cfg.deep_layers[l]
             d[f"Deep-part/mlp{l}/weights"] = w[:k_prev, :n]
             d[f"Deep-part/mlp{l}/biases"] = b[:n]
+            if cfg.batch_norm:
+                ob, N = self.off_bn[l], self.N[l]
+                d[f"Deep-part/bn_{l}/beta"] = dense[ob + N:ob + N + n]
+                d[f"Deep-part/bn_{l}/gamma"] = dense[ob:ob + n]
+                if moving is not None:
+                    om = self.off_mov[l]
+                    d[f"Deep-part/bn_{l}/moving_mean"] = moving[om:om + n]
+                    d[f"Deep-part/bn_{l}/moving_variance"] = moving[om + N:om + N + n]
             k_prev = n
         w, b = self._layer_views(dense, self.L)
         d["Deep-part/deep_out/weights"] = w[:k_prev, :]

@@ -41,6 +41,9 @@ int dfm_version(void);
 #define DFM_TABLE_LAZY 0        /* touched rows only (sparse-gradient path)            */
 #define DFM_TABLE_DENSE_EXACT 1 /* every row every step, g = sparse + l2*row (HVD.py:266-267) */
 
+#define DFM_LOSS_LOG 0
+#define DFM_LOSS_SQUARE 1
+
 #define DFM_MAX_LAYERS 6
 
 typedef struct {
@@ -59,22 +62,32 @@ typedef struct {
   float momentum;          /* Momentum                                                      */
   float ftrl_lr_power, ftrl_l1, ftrl_l2;
   uint64_t seed;           /* dropout stream                                                */
+  int32_t batch_norm;      /* --batch_norm: FC -> ReLU -> BN -> dropout (HVD.py:224-235,306-328) */
+  int32_t loss_type;       /* DFM_LOSS_LOG (HVD.py:264) or DFM_LOSS_SQUARE: mean (sigmoid(y) - label)^2 */
+  float bn_decay;          /* --batch_norm_decay, moving-average decay                      */
+  float bn_eps;            /* 1e-3, tf.contrib.layers.batch_norm default                    */
 } dfm_engine_config;
 
 /* Caller-owned fp32 device tensors (parameters and their optimizer slots).
  * dense* are flat vectors laid out as
  *   [P_0 | P_1 | ... | P_{L-1} | P_out | fm_bias],  P_l = [K_l + 1, N_l] row-major,
- * rows 0..K_l-1 = Deep-part/mlp{l}/weights, row K_l = .../biases (P_out: deep_out). */
+ * rows 0..K_l-1 = Deep-part/mlp{l}/weights, row K_l = .../biases (P_out: deep_out).
+ * With batch_norm the vector is [P_0 | ... | P_{L-1} | BN_0 | ... | BN_{L-1} | P_out | fm_bias] with
+ * BN_l = [gamma (N_l) | beta (N_l)] (Deep-part/bn_{l}/gamma, beta), and bn_moving holds, per layer,
+ * [moving_mean (N_l) | moving_variance (N_l)]; dfm_engine_layout reports the offsets. */
 typedef struct {
   float* fm_w;    float* fm_w_s0;  float* fm_w_s1;    /* [V]        */
   float* fm_v;    float* fm_v_s0;  float* fm_v_s1;    /* [V, K]     */
   float* dense;   float* dense_s0; float* dense_s1;   /* [n_dense]  */
+  float* bn_moving;                                   /* [2 * sum N_l] or NULL without batch_norm */
 } dfm_engine_tensors;
 
 int dfm_engine_create(const dfm_engine_config* cfg, const dfm_engine_tensors* tensors, void** engine);
 int dfm_engine_destroy(void* engine);
 /* offsets[L+2] (P_0..P_out, fm_bias) in elements, pitches[L+1] of the activation buffers. */
 int dfm_engine_layout(void* engine, long long* offsets, int* pitches, int* n_dense, int* batch_pad);
+/* batch_norm: per hidden layer, offset of [gamma | beta] in `dense` and of [moving_mean | moving_variance] in bn_moving. */
+int dfm_engine_bn_layout(void* engine, long long* dense_offsets, long long* moving_offsets);
 /* Step scalars live on the device (graph-replay safe): valid rows, lr, train flag;
  * step >= 0 also resets the 1-based optimizer step counter. */
 int dfm_engine_set_state(void* engine, int count, float lr, int train, int step, dfm_stream_t stream);

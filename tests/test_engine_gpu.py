@@ -282,3 +282,117 @@ def test_out_of_range_ids_are_clamped_and_counted():
 def FusedEngineRef(cfg, m, ids, vals, labels):
     with torch.no_grad():
         return torch.nn.functional.binary_cross_entropy_with_logits(m(ids, vals), labels, reduction="sum").item()
+
+
+# ---------------------------------------------------------------------------------------------
+# batch norm (FC -> ReLU -> BN -> dropout, HVD.py:224-235 + 306-328) and square loss on the fused path
+# ---------------------------------------------------------------------------------------------
+def _setup_bn(B, layers, loss_type="log_loss", V=5000, Ke=32, F=39, lr=1.0):
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.runtime.engine import FusedEngine
+    cfg = DeepFMConfig(field_size=F, feature_size=V, embedding_size=Ke, deep_layers=layers,
+                       dropout_keep=[1.0] * len(layers), l2_reg=0.0, batch_norm=True, batch_norm_decay=0.9,
+                       loss_type=loss_type)
+    m = DeepFM(cfg, seed=1).cuda()
+    g = torch.Generator(device="cuda").manual_seed(9)
+    with torch.no_grad():
+        m.fm_v.mul_(30); m.fm_w.mul_(30)
+        for l in range(len(layers)):
+            m.mlp_b[l].uniform_(-0.1, 0.1)
+            m.bn_gamma[l].copy_(0.5 + torch.rand(layers[l], device="cuda", generator=g))
+            m.bn_beta[l].copy_(0.2 * torch.randn(layers[l], device="cuda", generator=g))
+            getattr(m, f"bn_mean_{l}").copy_(0.1 * torch.rand(layers[l], device="cuda", generator=g))
+            getattr(m, f"bn_var_{l}").copy_(0.5 + torch.rand(layers[l], device="cuda", generator=g))
+        m.out_b.fill_(0.05); m.fm_bias.fill_(-0.3)
+    eng = FusedEngine(cfg, batch_max=B, optimizer="GD", lr=lr, seed=7)
+    eng.load_from_module(m)
+    ids = torch.randint(1, V, (B, F), device="cuda", generator=g, dtype=torch.int64)
+    ids[:, :13] = torch.arange(1, 14, device="cuda")
+    vals = torch.rand(B, F, device="cuda", generator=g)
+    vals[:, 13:] = 1.0
+    labels = (torch.rand(B, device="cuda", generator=g) < 0.3).float()
+    return cfg, m, eng, ids, vals, labels
+
+
+def _emulated_logits_bn(m, ids, vals, training):
+    """Oracle with the engine's rounding points: bf16 a = relu(.), fp32 statistics of the rounded a, bf16 BN output."""
+    from deepfm_b200.models.deepfm import BN_EPS
+    y_w, y_v, e = m.fm_terms(ids, vals)
+    h = _rt(e.reshape(e.shape[0], -1))
+    for l in range(len(m.cfg.deep_layers)):
+        a = _rt(torch.relu(h @ _rt(m.mlp_w[l]) + m.mlp_b[l]))
+        if training:
+            mean, var = a.mean(0), a.var(0, unbiased=False)
+        else:
+            mean, var = getattr(m, f"bn_mean_{l}"), getattr(m, f"bn_var_{l}")
+        h = _rt((a - mean) * torch.rsqrt(var + BN_EPS) * m.bn_gamma[l] + m.bn_beta[l])
+    return m.fm_bias + y_w + y_v + (h @ m.out_w).view(-1) + m.out_b
+
+
+@pytest.mark.parametrize("B,layers", [(256, [256, 128, 64]), (300, [100, 50])])
+def test_batch_norm_inference_uses_moving_statistics(B, layers):
+    cfg, m, eng, ids, vals, labels = _setup_bn(B, layers)
+    prob = eng.forward(ids.int().contiguous(), vals, labels)
+    with torch.no_grad():
+        logits = m(ids, vals, training=False)
+    torch.cuda.synchronize()
+    assert _rel(eng.buffer("logit")[:B], logits) < 2e-2
+    torch.testing.assert_close(prob, torch.sigmoid(logits), atol=1e-2, rtol=0)
+    eng.close()
+
+
+@pytest.mark.parametrize("B,layers,loss_type", [(256, [256, 128, 64], "log_loss"), (300, [100, 50], "log_loss"),
+                                                (256, [128, 64], "square_loss")])
+def test_batch_norm_training_step_equals_autograd(B, layers, loss_type):
+    cfg, m, eng, ids, vals, labels = _setup_bn(B, layers, loss_type)
+    before = {k: v.clone() for k, v in eng.variables().items()}
+    eng.train_step(ids.int().contiguous(), vals, labels)
+    torch.cuda.synchronize()
+    logits = _emulated_logits_bn(m, ids, vals, training=True)
+    m.loss(logits, labels).backward()
+    loss_ref = (m.data_loss(logits, labels) * B).item()
+    assert abs(eng.read_state()["loss_sum"] - loss_ref) < 2e-2 * abs(loss_ref) + 1e-3
+    touched = torch.zeros(cfg.feature_size, dtype=torch.bool, device="cuda")
+    touched[ids.unique()] = True
+    for name, p in m.trainable_tf_variables().items():
+        got = before[name] - eng.variables()[name]       # GD, lr = 1
+        ref = p.grad
+        if name in ("fm_w", "fm_v"):
+            ref = torch.where(touched if name == "fm_w" else touched[:, None], ref, torch.zeros_like(ref))
+        assert _rel(got, ref) < 3e-2, name
+    # moving averages moved towards the batch statistics (decay 0.9), like contrib batch_norm with updates_collections=None
+    with torch.no_grad():
+        m2 = type(m)(cfg, seed=1).cuda()
+        m2.load_tf_variables({k: v for k, v in before.items()})
+        m2(ids, vals, training=True)
+    for l in range(len(layers)):
+        for stat in ("moving_mean", "moving_variance"):
+            k = f"Deep-part/bn_{l}/{stat}"
+            torch.testing.assert_close(eng.variables()[k], m2.tf_variables()[k], rtol=3e-2, atol=3e-3)
+    eng.close()
+
+
+def test_square_loss_without_batch_norm():
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.runtime.engine import FusedEngine
+    B, V, layers = 256, 5000, [128, 64, 32]
+    cfg = DeepFMConfig(39, V, 32, layers, [1.0] * 3, l2_reg=0.0, loss_type="square_loss")
+    m = DeepFM(cfg, seed=1).cuda()
+    with torch.no_grad():
+        m.fm_v.mul_(30); m.fm_w.mul_(30)
+    eng = FusedEngine(cfg, batch_max=B, optimizer="GD", lr=1.0, seed=7)
+    eng.load_from_module(m)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    ids = torch.randint(1, V, (B, 39), device="cuda", generator=g, dtype=torch.int64)
+    vals = torch.rand(B, 39, device="cuda", generator=g)
+    labels = (torch.rand(B, device="cuda", generator=g) < 0.3).float()
+    before = {k: v.clone() for k, v in eng.variables().items()}
+    eng.train_step(ids.int().contiguous(), vals, labels)
+    torch.cuda.synchronize()
+    logits = _emulated_logits(m, ids, vals)
+    m.loss(logits, labels).backward()
+    ref_loss = ((torch.sigmoid(logits) - labels) ** 2).sum().item()
+    assert abs(eng.read_state()["loss_sum"] - ref_loss) < 2e-2 * ref_loss + 1e-3
+    for name in ("Deep-part/mlp0/weights", "Deep-part/deep_out/weights", "fm_bias"):
+        assert _rel(before[name] - eng.variables()[name], dict(m.tf_variables())[name].grad) < 2e-2, name
+    eng.close()
