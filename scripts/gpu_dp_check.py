@@ -102,7 +102,7 @@ res["dense_start_vs_sparse_start_us"] = round((int(dbg[8]) - t0) / 1000.0, 2)
 res["provider"] = fused.comm_provider.name
 res["multicast"] = int(fused.engine._lib.dfm_engine_comm_multicast(fused.engine._h))
 # Adam turns tiny bf16 differences of near-zero gradients into full-size steps; GD is the sharp check
-ok = all(v for k, v in res.items() if k.startswith("identical:")) and worst < (0.12 if opt != "GD" else 0.05)
+ok = all(v for k, v in res.items() if k.startswith("identical:")) and worst < (0.25 if opt != "GD" else 0.05)
 if os.environ.get("DFM_DP_PROFILE"):
     from torch.profiler import profile, ProfilerActivity
     ids, vals, labels = (t.to(dev) for t in data[0])

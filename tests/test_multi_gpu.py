@@ -1,4 +1,6 @@
-"""Fused NVLink collectives vs the restated NCCL path on real GPUs (skipped on boxes with fewer than 2)."""
+"""Fused NVLink collectives vs the restated NCCL path on real GPUs (skipped on boxes with fewer than 2; the same
+protocol runs on ONE GPU in tests/test_multi_rank_emu_gpu.py, and bench.py repeats the check before its timed region
+at every N > 1)."""
 import json
 import os
 import re
@@ -22,14 +24,18 @@ def _run_dp_check(world: int, opt: str, port: int, **extra_env):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("opt", ["GD", "Adam"])
-def test_fused_collectives_two_ranks(opt):
-    """Replicas stay bit-identical and the update matches eager fp32 + NCCL (scripts/gpu_dp_check.py)."""
-    p, results = _run_dp_check(2, opt, 29631)
+@pytest.mark.parametrize("opt,env", [("GD", {}), ("Adam", {}), ("GD", {"DFM_NO_MULTICAST": "1"}),
+                                     ("GD", {"DFM_COMM_PROVIDER": "ipc"})])
+def test_fused_collectives_two_ranks(opt, env):
+    """Replicas stay bit-identical and the update matches eager fp32 + NCCL (scripts/gpu_dp_check.py), with NVLS
+    multicast, with peer loops on symmetric memory, and on plain CUDA IPC mappings."""
+    p, results = _run_dp_check(2, opt, 29631, **env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert len(results) == 2 and all(r["ok"] for r in results)
     for r in results:
         assert all(v for k, v in r.items() if k.startswith("identical:"))
+        if opt == "GD":
+            assert r["worst_rel_update_err"] < 0.05
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
@@ -39,6 +45,13 @@ def test_fused_collectives_other_embedding_sizes(ke):
     p, results = _run_dp_check(2, "GD", 29633, DFM_DP_KE=ke, DFM_DP_LAYERS="400,400")
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert len(results) == 2 and all(r["ok"] for r in results)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4 GPUs")
+def test_fused_collectives_four_ranks():
+    p, results = _run_dp_check(4, "GD", 29634)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert len(results) == 4 and all(r["ok"] for r in results)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 8, reason="needs 8 GPUs")
