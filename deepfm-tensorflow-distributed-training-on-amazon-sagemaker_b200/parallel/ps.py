@@ -37,7 +37,7 @@ from ..utils.optimizers import TFOptimizer
 
 # request codes (header = int64[4]: op, variable index, n, aux)
 OP_PULL_ROWS, OP_PULL, OP_PUSH_ROWS, OP_PUSH, OP_SET, OP_STEP, OP_GET_SLOTS, OP_INIT_DONE, OP_IS_INIT, \
-    OP_DONE, OP_N_DONE, OP_ASSIGN = range(12)
+    OP_DONE, OP_N_DONE, OP_ASSIGN, OP_PULL_DENSE, OP_PUSH_DENSE = range(14)
 
 TABLES = ("fm_w", "fm_v")
 
@@ -67,6 +67,8 @@ class ParameterServer:
             if "moving_" not in n:
                 self.opt.ensure_slots(n, t)
         self.mode = table_update_mode
+        # everything here that is not an embedding table, in variable order: one message moves all of it
+        self.dense_names = [n for n in self.vars if n not in TABLES]
         self.initialised = False
         self.done = 0
         self.global_step = 0
@@ -103,6 +105,25 @@ class ParameterServer:
                 g = torch.empty_like(self.vars[name])
                 dist.recv(g, src=src)
                 self.opt.apply_dense(name, self.vars[name], g)
+                self.applies += 1
+            elif op == OP_PULL_DENSE:
+                # every dense variable (and BN moving statistic) of this task as ONE flat message
+                flat = torch.cat([self.vars[k].reshape(-1) for k in self.dense_names]) if self.dense_names \
+                    else torch.zeros(0)
+                dist.send(flat, dst=src)
+            elif op == OP_PUSH_DENSE:
+                # one flat message: gradients of the trainable dense variables, new values of the moving statistics
+                flat = torch.empty(sum(self.vars[k].numel() for k in self.dense_names))
+                dist.recv(flat, src=src)
+                o = 0
+                for k in self.dense_names:
+                    t = self.vars[k]
+                    piece = flat[o:o + t.numel()].view_as(t)
+                    o += t.numel()
+                    if "moving_" in k:
+                        t.copy_(piece)                   # assigned, not optimised
+                    else:
+                        self.opt.apply_dense(k, t, piece)
                 self.applies += 1
             elif op in (OP_SET, OP_ASSIGN):
                 t = torch.empty_like(self.vars[name])
@@ -184,6 +205,35 @@ class PSClient:
         dist.recv(t, src=dst)
         return t
 
+    def dense_names_on(self, ps: int) -> List[str]:
+        return [n for n in self.names if self.place[n] == ps and n not in TABLES]
+
+    def pull_dense_all(self) -> Dict[str, torch.Tensor]:
+        """All dense variables and BN statistics: one request + one flat reply per PS task."""
+        out: Dict[str, torch.Tensor] = {}
+        for ps in range(self.n_ps):
+            names = self.dense_names_on(ps)
+            if not names:
+                continue
+            dist.send(_hdr(OP_PULL_DENSE), dst=ps)
+            flat = torch.empty(sum(int(np.prod(self.shapes[n])) for n in names), dtype=torch.float32)
+            dist.recv(flat, src=ps)
+            o = 0
+            for n in names:
+                k = int(np.prod(self.shapes[n]))
+                out[n] = flat[o:o + k].view(self.shapes[n])
+                o += k
+        return out
+
+    def push_dense_all(self, values: Dict[str, torch.Tensor]) -> None:
+        """``values[name]`` = gradient of a trainable dense variable, or the new value of a moving statistic."""
+        for ps in range(self.n_ps):
+            names = self.dense_names_on(ps)
+            if not names:
+                continue
+            dist.send(_hdr(OP_PUSH_DENSE), dst=ps)
+            dist.send(torch.cat([values[n].detach().reshape(-1).float() for n in names]), dst=ps)
+
     def step_all(self) -> int:
         """Tells every PS task one train_op finished; returns the global step (kept on task 0)."""
         gs = 0
@@ -220,8 +270,8 @@ class PSWorker:
     def pull_dense(self) -> None:
         tv = self.model.tf_variables()
         with torch.no_grad():
-            for n in self.dense_names + self.stat_names:
-                tv[n].copy_(self.c.pull(n))
+            for n, t in self.c.pull_dense_all().items():
+                tv[n].copy_(t)
 
     def pull_all(self) -> None:
         tv = self.model.tf_variables()
@@ -242,10 +292,8 @@ class PSWorker:
         loss.backward()
         self.c.push_rows("fm_w", uniq, w_rows.grad)
         self.c.push_rows("fm_v", uniq, v_rows.grad)
-        for n in self.dense_names:
-            self.c.push(n, tv[n].grad)
-        for n in self.stat_names:                      # BN moving averages are assigned, not optimised
-            self.c.set(n, tv[n], assign=True)
+        # dense gradients and the BN moving averages (assigned, not optimised) travel as one message per PS task
+        self.c.push_dense_all({**{n: tv[n].grad for n in self.dense_names}, **{n: tv[n] for n in self.stat_names}})
         self.global_step = self.c.step_all()
         self.last_loss = float(loss.detach())
         return self.last_loss
@@ -351,12 +399,21 @@ def run_ps(flags, env) -> int:
         while not client.ask(OP_IS_INIT):                # "others join once the master is up" (README.md:63)
             time.sleep(0.05)
 
+    # SageMaker pipe mode (PS.py:137-151): the channels are FIFOs /opt/ml/input/data/<channel>_<epoch>, read as streams
+    pipe = bool(flags.pipe_mode)
+
+    def channel_fifo(name: str, epoch: int = 0) -> str:
+        return os.path.join(os.environ.get("SM_INPUT_DATA_DIR", "/opt/ml/input/data"), f"{name}_{epoch}")
+
+    train_channel = flags.training_channel_name or "training"
+    eval_channel = flags.evaluation_channel_name or "evaluation"
+
     def evaluate(files) -> Dict[str, float]:
         worker.pull_all()
         worker.model.eval()
         auc, loss_sum, n = StreamingAUC(200), 0.0, 0
         loader = BatchLoader(files, cfg.field_size, flags.batch_size, drop_remainder=flags.drop_remainder_eval,
-                             ids_dtype=torch.int64, num_workers=flags.loader_threads)
+                             ids_dtype=torch.int64, num_workers=flags.loader_threads, streaming=pipe)
         with torch.no_grad():
             for hb in loader:
                 logits = worker.model(hb.feat_ids, hb.feat_vals, training=False)
@@ -366,16 +423,23 @@ def run_ps(flags, env) -> int:
         loader.close()
         return {"auc": auc.result(), "loss": loss_sum / max(n, 1), "examples": n, "global_step": worker.global_step}
 
-    tr = sorted(glob.glob(f"{flags.training_data_dir}/**/tr*.tfrecords", recursive=True)) if flags.training_data_dir else []
-    va = sorted(glob.glob(f"{flags.val_data_dir}/**/va*.tfrecords", recursive=True)) if flags.val_data_dir else []
+    if pipe:
+        tr = [channel_fifo(train_channel, e) for e in range(flags.num_epochs)]       # one FIFO per epoch
+        va = [channel_fifo(eval_channel, 0)]
+        te = [channel_fifo(eval_channel, 0)]
+    else:
+        tr = sorted(glob.glob(f"{flags.training_data_dir}/**/tr*.tfrecords", recursive=True)) if flags.training_data_dir else []
+        va = sorted(glob.glob(f"{flags.val_data_dir}/**/va*.tfrecords", recursive=True)) if flags.val_data_dir else []
+        te = sorted(glob.glob(f"{flags.val_data_dir}/**/te*.tfrecords", recursive=True)) if flags.val_data_dir else []
     if flags.task_type == "train":
         if not tr:
             raise SystemExit(f"no tr*.tfrecords under --training_data_dir {flags.training_data_dir!r}")
         shard = ps_shard(flags.enable_s3_shard, flags.hosts, flags.current_host)      # PS.py:153-156
         if shard == (1, 0) and len(flags.hosts) <= 1 and n_workers > 1 and not flags.enable_s3_shard:
             shard = (n_workers, index)       # several workers on one host: split the stream between them
-        loader = BatchLoader(tr, cfg.field_size, flags.batch_size, num_epochs=flags.num_epochs, drop_remainder=True,
-                             shard_n=shard[0], shard_i=shard[1], ids_dtype=torch.int64, num_workers=flags.loader_threads)
+        loader = BatchLoader(tr, cfg.field_size, flags.batch_size, num_epochs=1 if pipe else flags.num_epochs,
+                             drop_remainder=True, shard_n=shard[0], shard_i=shard[1], ids_dtype=torch.int64,
+                             num_workers=flags.loader_threads, streaming=pipe)
         t_start = t_log = time.time()
         last_eval, steps = t_start, 0
         for hb in loader:
@@ -407,9 +471,32 @@ def run_ps(flags, env) -> int:
             if flags.servable_model_dir:
                 worker.pull_all()
                 print(tag, "servable model exported to", export_servable(worker.model, flags.servable_model_dir), flush=True)
-        client.broadcast_simple(OP_DONE)
-    elif flags.task_type == "eval" and chief:
-        print(tag, "eval:", evaluate(va), flush=True)
+    elif chief:
+        # eval / infer / export run on the chief against the parameters the servers hold (restored above), like
+        # Estimator.evaluate / predict / export_savedmodel in PS.py:522-551; the other workers only say goodbye
+        if flags.task_type == "eval":
+            print(tag, "eval:", evaluate(va), flush=True)
+        elif flags.task_type == "infer":                 # PS.py:526-533: one "%f" line per example into pred.txt
+            worker.pull_all()
+            worker.model.eval()
+            out_path = os.path.join(flags.val_data_dir or ".", "pred.txt")
+            loader = BatchLoader(te, cfg.field_size, flags.batch_size, drop_remainder=flags.drop_remainder_eval,
+                                 ids_dtype=torch.int64, num_workers=flags.loader_threads, streaming=pipe)
+            n = 0
+            with open(out_path, "w") as fo, torch.no_grad():
+                for hb in loader:
+                    prob = torch.sigmoid(worker.model(hb.feat_ids, hb.feat_vals, training=False))
+                    for pv in prob.tolist():
+                        fo.write("%f\n" % pv)
+                    n += hb.count
+            loader.close()
+            print(tag, f"{n} predictions written to {out_path}", flush=True)
+        elif flags.task_type == "export":                # PS.py:535-551
+            if not flags.servable_model_dir:
+                raise SystemExit("--task_type export needs --servable_model_dir")
+            worker.pull_all()
+            print(tag, "servable model exported to", export_servable(worker.model, flags.servable_model_dir), flush=True)
+    client.broadcast_simple(OP_DONE)       # every worker, whatever the task: lets the parameter servers finish
 
     dist.destroy_process_group()
     return 0

@@ -113,3 +113,31 @@ def test_launch_parameter_server_two_instances(tmp_path, val_tfrecords):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "[ps 0] serving" in r.stdout and "[ps 1] serving" in r.stdout and "'auc'" in r.stdout
     assert os.path.exists(tmp_path / "model" / "checkpoint")
+
+
+def test_parameter_server_infer_export_and_pipe(tmp_path, val_tfrecords):
+    """PS.py:137-151 (pipe input) and PS.py:522-551 (eval / infer -> pred.txt / export-only) in parameter-server mode:
+    train through FIFOs, then infer and export from the checkpoint the chief wrote."""
+    _write_split(tmp_path, val_tfrecords)
+    recs = list(T.iter_records(val_tfrecords))[1200:1500]
+    with T.TFRecordWriter(str(tmp_path / "val" / "te_0.tfrecords")) as w:
+        for r in recs:
+            w.write(r)
+    common = HP + [f"model_dir={tmp_path / 'model'}"]
+    r = _launch(["--distribution", "parameter_server", "--instance_count", "1", "--input_mode", "Pipe",
+                 "--pipe_root", str(tmp_path), "--master_port", "29574", "--hyperparameters"] + common +
+                ["training_channel_name=training", "evaluation_channel_name=evaluation",
+                 "--channels", f"training={tmp_path / 'train'}", f"evaluation={tmp_path / 'val'}"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert os.path.exists(tmp_path / "model" / "checkpoint")
+    r = _launch(["--distribution", "parameter_server", "--instance_count", "1", "--master_port", "29575",
+                 "--hyperparameters"] + common + ["task_type=infer",
+                 "--channels", f"training={tmp_path / 'train'}", f"evaluation={tmp_path / 'val'}"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    preds = [float(x) for x in open(tmp_path / "val" / "pred.txt").read().split()]
+    assert len(preds) == 300 and all(0.0 <= p <= 1.0 for p in preds)
+    r = _launch(["--distribution", "parameter_server", "--instance_count", "1", "--master_port", "29576",
+                 "--hyperparameters"] + common + ["task_type=export", f"servable_model_dir={tmp_path / 'servable'}",
+                 "--channels", f"training={tmp_path / 'train'}", f"evaluation={tmp_path / 'val'}"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert any((tmp_path / "servable").iterdir())
