@@ -1,4 +1,4 @@
-// ThreadSanitizer driver for the host data layer: the reader thread, the parser pool and the
+// ThreadSanitizer driver for the host data layer: the batcher thread, the worker pool (framing-index and parse tasks) and the
 // consumer of libdfm_io's batch loader run over a synthetic file with a small ring, twice (eager release and
 // release lagging two batches behind, the way Trainer.train_batches holds slots), and the stream is checked.
 //   g++ -std=c++17 -O1 -g -fsanitize=thread -msse4.2 -pthread -Iinclude csrc/bench/io_tsan_driver.cc csrc/io/*.cc -o build/io_tsan && build/io_tsan
@@ -12,7 +12,7 @@
 int main() {
   const char* path = "/tmp/dfm_tsan.tfrecords";
   const int F = 39, B = 64, slots = 4;
-  const int64_t n = 64 * 50 + 17;
+  const int64_t n = 64 * 200 + 17;   // ~4 MB: four framing-index ranges walked in parallel
   if (dfio_generate_synthetic(path, n, F, 5000, 13, 7, 0.25, 1.05) != n) { printf("generate: %s\n", dfio_last_error()); return 1; }
   for (int lag = 0; lag <= 2; lag += 2) {
     std::vector<std::vector<int32_t>> ids(slots, std::vector<int32_t>(B * F));
@@ -41,7 +41,7 @@ int main() {
     while (!held.empty()) { dfio_loader_release(L, held.front()); held.pop_front(); }
     dfio_loader_destroy(L);
     printf("lag %d: %d batches, checksum %.3f\n", lag, batches, checksum);
-    if (batches != 100) { printf("expected 100 batches\n"); return 1; }
+    if (batches != 400) { printf("expected 400 batches\n"); return 1; }
   }
   printf("io tsan driver ok\n");
   return 0;

@@ -29,7 +29,19 @@ class RecordSource {
   virtual int next(const uint8_t** data, uint64_t* len) = 0;
   virtual bool stable_pointers() const = 0;
   virtual uint64_t bytes_consumed() const = 0;
+  // mapped files only: the whole file as one byte range (lets several threads walk the framing of disjoint ranges)
+  virtual bool mapping(const uint8_t** base, size_t* size) const { return false; }
 };
+
+// Walks the TFRecord framing of base[pos, limit_start) (records that START before limit_start): appends
+// {payload offset, payload length}; returns the position after the last record walked, or (size_t)-1 on a framing
+// error (message set).  verify_len_crc: check the CRC of every length field.
+struct RecSpan { uint64_t off; uint32_t len; };
+size_t walk_framing(const uint8_t* base, size_t size, size_t pos, size_t limit_start, bool verify_len_crc,
+                    std::vector<RecSpan>* out, const char* path);
+// First position >= from (and < to) that looks like a record start: its length CRC checks out and so does the next
+// record's (or the file ends there).  (size_t)-1 if none.  A guess: the caller confirms it against the true chain.
+size_t find_record_start(const uint8_t* base, size_t size, size_t from, size_t to);
 
 // verify_mapped / verify_stream: check both CRCs of every record for mapped files / streams.
 std::unique_ptr<RecordSource> open_source(const std::string& path, bool verify_mapped, bool verify_stream,
@@ -40,8 +52,9 @@ std::unique_ptr<RecordSource> open_source(const std::string& path, bool verify_m
 // ---------------------------------------------------------------------------
 // Decodes label / ids / values from a serialized tf.train.Example.  Keys may
 // come in any order; lists may be packed or unpacked.  Returns 0 or -1.
+// max_id > 0: ids must lie in [0, max_id) (what TF's embedding_lookup enforces on CPU); a violation is an error.
 int parse_example(const uint8_t* p, uint64_t len, int field_size, void* ids_out, bool ids_i32,
-                  float* vals_out, float* label_out);
+                  float* vals_out, float* label_out, uint64_t max_id = 0);
 // Appends the serialized Example to `out`.
 void encode_example(float label, const int64_t* ids, const float* vals, int n, bool packed,
                     std::vector<uint8_t>& out);

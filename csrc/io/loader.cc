@@ -2,14 +2,18 @@
 // prefetch, the order of the reference's input_fn (HVD.py:127-159), as a native
 // pipeline:
 //
-//   reader thread   walks the record framing of every file of every epoch, applies the
-//                   record-level shard (index % n == i), groups kept records into batches
-//                   and hands each batch to the workers in row ranges
-//   worker threads  verify + decode Examples straight into the caller's (pinned) slot
+//   index tasks     (mapped files) the record framing of disjoint 1 MiB byte ranges is walked by the worker pool in
+//                   parallel: a range that does not start at byte 0 first looks for a plausible record start (two
+//                   consecutive length CRCs that check out) and the batcher confirms it against the true chain --
+//                   the previous range's end -- re-walking the range itself on the rare false guess
+//   batcher thread  consumes the ranges in order, applies the record-level shard (index % n == i), groups kept
+//                   records into batches and hands each batch to the workers in row ranges; FIFOs / stdin
+//                   (SageMaker pipe mode) are read sequentially by this thread instead
+//   parse tasks     verify CRCs + decode Examples straight into the caller's (pinned) slot, check the id range
 //   consumer        dfio_loader_next() returns slots strictly in stream order
 //
 // Slots form a ring: batch b lives in slot b % num_slots, so "prefetch depth" is
-// num_slots - 1 and the consumer's release() is what lets the reader run ahead.
+// num_slots - 1 and the consumer's release() is what lets the batcher run ahead.
 #include <atomic>
 #include <condition_variable>
 #include <deque>
@@ -22,27 +26,49 @@ namespace dfio {
 namespace {
 
 constexpr uint64_t kNoOffset = ~0ull;
+constexpr size_t kIndexChunk = 1u << 20;
 
 struct Rec {
   const uint8_t* p;   // payload (resolved from `off` once the arena is final)
   uint32_t len;
+  uint32_t seg;       // index into BatchWork::segs (which file the record came from)
   uint64_t off;       // payload offset inside BatchWork::arena, or kNoOffset for mapped records
 };
 
+struct FileSeg {
+  std::shared_ptr<RecordSource> src;   // keeps a mapping alive while the batch points into it
+  const uint8_t* base = nullptr;       // mapped files: start of the mapping (for error offsets)
+  std::string path;
+};
+
 // One batch worth of records.  For mapped files the records point into the
-// mapping (kept alive by `maps`); for streams they point into `arena`.
+// mapping (kept alive by `segs`); for streams they point into `arena`.
 struct BatchWork {
   int slot = 0;
   int count = 0;
   std::vector<Rec> recs;
   std::vector<uint8_t> arena;
-  std::vector<std::shared_ptr<RecordSource>> maps;
+  std::vector<FileSeg> segs;
   std::atomic<int> remaining{0};
 };
 
+// A byte range of a mapped file whose framing one worker walks.
+struct Chunk {
+  const uint8_t* base = nullptr;
+  size_t size = 0, begin = 0, end = 0;
+  bool verify = false;
+  const char* path = "";
+  size_t start = static_cast<size_t>(-1);   // first record start found in [begin, end) (guess unless begin == 0)
+  size_t stop = 0;                          // position after the last record walked
+  std::vector<RecSpan> recs;
+  std::string err;
+  bool done = false;                        // guarded by Loader::mu_
+};
+
 struct Task {
-  std::shared_ptr<BatchWork> bw;
-  int row0, row1;
+  std::shared_ptr<BatchWork> bw;            // parse task: rows [row0, row1) of this batch
+  int row0 = 0, row1 = 0;
+  std::shared_ptr<Chunk> chunk;             // index task
 };
 
 enum SlotState { kFree = 0, kFilling = 1, kReady = 2, kInUse = 3 };
@@ -74,6 +100,7 @@ class Loader {
     cv_slot_.notify_all();
     cv_task_.notify_all();
     cv_ready_.notify_all();
+    cv_chunk_.notify_all();
     if (reader_.joinable()) reader_.join();
     for (auto& w : workers_) w.join();
   }
@@ -139,6 +166,7 @@ class Loader {
     cv_ready_.notify_all();
     cv_slot_.notify_all();
     cv_task_.notify_all();
+    cv_chunk_.notify_all();
   }
 
   // Blocks until the ring slot of batch `produced_` is free, then queues its tasks.
@@ -155,19 +183,130 @@ class Loader {
     const int chunk = std::max(64, (bw->count + cfg_.num_workers - 1) / cfg_.num_workers);
     int ntasks = (bw->count + chunk - 1) / chunk;
     bw->remaining.store(ntasks);
-    for (int r = 0; r < bw->count; r += chunk) tasks_.push_back(Task{bw, r, std::min(bw->count, r + chunk)});
+    for (int r = 0; r < bw->count; r += chunk) parse_tasks_.push_back(Task{bw, r, std::min(bw->count, r + chunk), nullptr});
     ++produced_;
     l.unlock();
     cv_task_.notify_all();
     return true;
   }
 
+  // ---- batcher -------------------------------------------------------------------------------
+  struct EpochState {
+    std::shared_ptr<BatchWork> bw;
+    int64_t idx = 0;          // record index within the epoch's concatenated stream
+  };
+
+  void new_batch(EpochState& es) {
+    es.bw = std::make_shared<BatchWork>();
+    es.bw->recs.reserve(cfg_.batch_size);
+  }
+
+  // the batch's reference to the file the next records come from
+  uint32_t seg_of(EpochState& es, const std::shared_ptr<RecordSource>& src, const uint8_t* base, const std::string& path) {
+    auto& segs = es.bw->segs;
+    if (segs.empty() || segs.back().src != src) segs.push_back(FileSeg{src, base, path});
+    return static_cast<uint32_t>(segs.size() - 1);
+  }
+
+  bool add_record(EpochState& es, const Rec& r) {
+    es.bw->recs.push_back(r);
+    if (static_cast<int>(es.bw->recs.size()) < cfg_.batch_size) return true;
+    if (!finish_and_submit(es.bw)) return false;
+    new_batch(es);
+    return true;
+  }
+
+  void index_chunk(Chunk& c) {
+    size_t pos = c.begin == 0 ? 0 : find_record_start(c.base, c.size, c.begin, c.end);
+    c.start = pos;
+    if (pos == static_cast<size_t>(-1)) {
+      c.stop = c.end;
+      return;
+    }
+    c.recs.reserve((c.end - pos) / 256 + 16);
+    const size_t stop = walk_framing(c.base, c.size, pos, c.end, c.verify, &c.recs, c.path);
+    if (stop == static_cast<size_t>(-1)) c.err = dfio_last_error();
+    c.stop = stop;
+  }
+
+  // Mapped file: ranges are indexed by the worker pool ahead of the batcher, which consumes them in order.
+  bool read_mapped(EpochState& es, const std::shared_ptr<RecordSource>& src, const uint8_t* base, size_t size,
+                   const std::string& path) {
+    const size_t n_chunks = (size + kIndexChunk - 1) / kIndexChunk;
+    const size_t window = static_cast<size_t>(std::max(2, cfg_.num_workers));
+    std::deque<std::shared_ptr<Chunk>> inflight;
+    size_t next_chunk = 0, expected = 0;      // `expected` = true start of the next record (the chain)
+    for (size_t ci = 0; ci < n_chunks; ++ci) {
+      while (next_chunk < n_chunks && inflight.size() < window) {
+        auto c = std::make_shared<Chunk>();
+        c->base = base; c->size = size; c->verify = cfg_.verify_crc != 0; c->path = path.c_str();
+        c->begin = next_chunk * kIndexChunk;
+        c->end = std::min(size, c->begin + kIndexChunk);
+        {
+          std::lock_guard<std::mutex> l(mu_);
+          index_tasks_.push_back(Task{nullptr, 0, 0, c});
+        }
+        cv_task_.notify_one();
+        inflight.push_back(c);
+        ++next_chunk;
+      }
+      std::shared_ptr<Chunk> c = inflight.front();
+      inflight.pop_front();
+      {
+        std::unique_lock<std::mutex> l(mu_);
+        cv_chunk_.wait(l, [&] { return stop_ || failed_ || c->done; });
+        if (stop_ || failed_) return false;
+      }
+      // the true first record of this range starts at `expected` if that lies inside it, else the range has none
+      const size_t truth = expected < c->end ? expected : static_cast<size_t>(-1);
+      if (c->start != truth) {                // wrong guess (or a record spanning the whole range): walk it here
+        c->recs.clear();
+        c->err.clear();
+        c->stop = expected;
+        if (truth != static_cast<size_t>(-1)) {
+          const size_t stop = walk_framing(base, size, truth, c->end, cfg_.verify_crc != 0, &c->recs, path.c_str());
+          if (stop == static_cast<size_t>(-1)) c->err = dfio_last_error();
+          c->stop = stop;
+        }
+      }
+      if (!c->err.empty()) {
+        fail(c->err);
+        return false;
+      }
+      expected = std::max(expected, c->stop);
+      for (const RecSpan& r : c->recs) {
+        if (es.idx++ % cfg_.shard_n != cfg_.shard_i) continue;
+        if (!add_record(es, Rec{base + r.off, r.len, seg_of(es, src, base, path), kNoOffset})) return false;
+      }
+    }
+    bytes_ += static_cast<int64_t>(size);
+    return true;
+  }
+
+  // FIFO / stdin: sequential; payloads are copied (their CRCs were checked by the stream source)
+  bool read_stream(EpochState& es, const std::shared_ptr<RecordSource>& src, const std::string& path) {
+    const uint8_t* d;
+    uint64_t n;
+    int r;
+    while ((r = src->next(&d, &n)) == 1) {
+      if (es.idx++ % cfg_.shard_n != cfg_.shard_i) continue;
+      const size_t off = es.bw->arena.size();
+      es.bw->arena.insert(es.bw->arena.end(), d, d + n);
+      if (!add_record(es, Rec{nullptr, static_cast<uint32_t>(n), seg_of(es, src, nullptr, path), off})) return false;
+      // (stop / failure are noticed in submit(), once per batch: no lock per record on this path)
+    }
+    bytes_ += static_cast<int64_t>(src->bytes_consumed());
+    if (r < 0) {
+      fail(dfio_last_error());
+      return false;
+    }
+    return true;
+  }
+
   void reader_main() {
-    const int B = cfg_.batch_size;
     for (int epoch = 0; epoch < cfg_.num_epochs; ++epoch) {
-      auto bw = std::make_shared<BatchWork>();
-      bw->recs.reserve(B);
-      int64_t idx = 0;  // record index within the epoch's concatenated stream
+      EpochState es;
+      new_batch(es);
       for (const auto& path : paths_) {
         std::shared_ptr<RecordSource> src(open_source(path, /*verify_mapped=*/false, /*verify_stream=*/cfg_.verify_crc != 0,
                                                         cfg_.streaming != 0).release());
@@ -175,38 +314,13 @@ class Loader {
           fail(dfio_last_error());
           return;
         }
-        const bool stable = src->stable_pointers();
-        if (stable) bw->maps.push_back(src);
-        const uint8_t* d;
-        uint64_t n;
-        int r;
-        while ((r = src->next(&d, &n)) == 1) {
-          if (idx++ % cfg_.shard_n != cfg_.shard_i) continue;
-          if (stable) {
-            bw->recs.push_back(Rec{d, static_cast<uint32_t>(n), kNoOffset});
-          } else {
-            // Streamed payloads are copied (their CRCs were checked by the stream source);
-            // offsets now, pointers once the arena stops growing.
-            const size_t off = bw->arena.size();
-            bw->arena.insert(bw->arena.end(), d, d + n);
-            bw->recs.push_back(Rec{nullptr, static_cast<uint32_t>(n), off});
-          }
-          if (static_cast<int>(bw->recs.size()) == B) {
-            if (!finish_and_submit(bw)) return;
-            bw = std::make_shared<BatchWork>();
-            bw->recs.reserve(B);
-            if (stable) bw->maps.push_back(src);
-          }
-          // (stop / failure are noticed in submit(), once per batch: no lock per record on the reader's path)
-        }
-        bytes_ += static_cast<int64_t>(src->bytes_consumed());
-        if (r < 0) {
-          fail(dfio_last_error());
-          return;
-        }
+        const uint8_t* base = nullptr;
+        size_t size = 0;
+        const bool ok = src->mapping(&base, &size) ? read_mapped(es, src, base, size, path) : read_stream(es, src, path);
+        if (!ok) return;
       }
-      if (!bw->recs.empty() && !cfg_.drop_remainder) {
-        if (!finish_and_submit(bw)) return;
+      if (!es.bw->recs.empty() && !cfg_.drop_remainder) {
+        if (!finish_and_submit(es.bw)) return;
       }
     }
     {
@@ -224,35 +338,53 @@ class Loader {
     return submit(bw);
   }
 
+  // ---- workers --------------------------------------------------------------------------------
+  std::string where(const BatchWork& bw, const Rec& rec) const {
+    const FileSeg& sg = bw.segs[rec.seg];
+    char buf[64] = "";
+    if (sg.base) snprintf(buf, sizeof(buf), ", record payload at byte offset %llu", (unsigned long long)(rec.p - sg.base));
+    return " (" + sg.path + buf + ")";
+  }
+
   void worker_main() {
     const int F = cfg_.field_size;
     const size_t id_sz = cfg_.ids_i32 ? 4 : 8;
+    const uint64_t max_id = cfg_.feature_size > 0 ? static_cast<uint64_t>(cfg_.feature_size) : 0;
     for (;;) {
       Task t;
       {
         std::unique_lock<std::mutex> l(mu_);
-        cv_task_.wait(l, [&] { return stop_ || failed_ || !tasks_.empty(); });
+        cv_task_.wait(l, [&] { return stop_ || failed_ || !parse_tasks_.empty() || !index_tasks_.empty(); });
         if (stop_ || failed_) return;
-        t = std::move(tasks_.front());
-        tasks_.pop_front();
+        auto& q = !parse_tasks_.empty() ? parse_tasks_ : index_tasks_;     // batches in flight first
+        t = std::move(q.front());
+        q.pop_front();
+      }
+      if (t.chunk) {
+        index_chunk(*t.chunk);
+        {
+          std::lock_guard<std::mutex> l(mu_);
+          t.chunk->done = true;
+        }
+        cv_chunk_.notify_all();
+        continue;
       }
       Slot& s = slots_[t.bw->slot];
       bool ok = true;
       for (int r = t.row0; r < t.row1 && ok; ++r) {
         const Rec& rec = t.bw->recs[r];
         if (cfg_.verify_crc && rec.off == kNoOffset) {  // mapped record: framing sits around the payload
-          uint32_t lcrc, dcrc;
-          memcpy(&lcrc, rec.p - 4, 4);
+          uint32_t dcrc;
           memcpy(&dcrc, rec.p + rec.len, 4);
-          if (mask_crc(crc32c(rec.p - 12, 8)) != lcrc || mask_crc(crc32c(rec.p, rec.len)) != dcrc) {
-            fail("TFRecord CRC mismatch (corrupt input)");
+          if (mask_crc(crc32c(rec.p, rec.len)) != dcrc) {
+            fail("TFRecord CRC mismatch (corrupt input)" + where(*t.bw, rec));
             ok = false;
             break;
           }
         }
         if (parse_example(rec.p, rec.len, F, static_cast<uint8_t*>(s.ids) + size_t(r) * F * id_sz,
-                          cfg_.ids_i32 != 0, s.vals + size_t(r) * F, s.labels + r) != 0) {
-          fail(dfio_last_error());
+                          cfg_.ids_i32 != 0, s.vals + size_t(r) * F, s.labels + r, max_id) != 0) {
+          fail(std::string(dfio_last_error()) + where(*t.bw, rec));
           ok = false;
         }
       }
@@ -273,8 +405,8 @@ class Loader {
   std::vector<std::string> paths_;
   std::vector<Slot> slots_;
   std::mutex mu_;
-  std::condition_variable cv_slot_, cv_task_, cv_ready_;
-  std::deque<Task> tasks_;
+  std::condition_variable cv_slot_, cv_task_, cv_ready_, cv_chunk_;
+  std::deque<Task> parse_tasks_, index_tasks_;
   int64_t produced_ = 0;    // batches handed to workers
   int64_t next_batch_ = 0;  // next batch the consumer gets
   bool reader_done_ = false, stop_ = false, failed_ = false;

@@ -92,6 +92,11 @@ class MappedSource final : public RecordSource {
   }
   bool stable_pointers() const override { return true; }
   uint64_t bytes_consumed() const override { return pos_; }
+  bool mapping(const uint8_t** base, size_t* size) const override {
+    *base = base_;
+    *size = size_;
+    return true;
+  }
 
  private:
   const uint8_t* base_;
@@ -100,6 +105,56 @@ class MappedSource final : public RecordSource {
   bool verify_;
   std::string path_;
 };
+
+}  // namespace
+
+static inline bool header_ok(const uint8_t* base, size_t size, size_t pos, uint64_t* n) {
+  if (size - pos < 16) return false;
+  uint32_t lcrc;
+  memcpy(n, base + pos, 8);
+  memcpy(&lcrc, base + pos + 8, 4);
+  if (*n > size - pos - 16) return false;
+  return mask_crc(crc32c(base + pos, 8)) == lcrc;
+}
+
+size_t find_record_start(const uint8_t* base, size_t size, size_t from, size_t to) {
+  for (size_t pos = from; pos < to && pos + 16 <= size; ++pos) {
+    uint64_t n, n2;
+    if (!header_ok(base, size, pos, &n)) continue;
+    const size_t nxt = pos + 16 + n;
+    if (nxt == size || header_ok(base, size, nxt, &n2)) return pos;
+  }
+  return static_cast<size_t>(-1);
+}
+
+size_t walk_framing(const uint8_t* base, size_t size, size_t pos, size_t limit_start, bool verify_len_crc,
+                    std::vector<RecSpan>* out, const char* path) {
+  while (pos < limit_start && pos < size) {
+    if (size - pos < 12) {
+      set_error("%s: truncated record header at offset %zu", path, pos);
+      return static_cast<size_t>(-1);
+    }
+    uint64_t n;
+    memcpy(&n, base + pos, 8);
+    if (verify_len_crc) {
+      uint32_t lcrc;
+      memcpy(&lcrc, base + pos + 8, 4);
+      if (mask_crc(crc32c(base + pos, 8)) != lcrc) {
+        set_error("%s: corrupt length CRC at offset %zu", path, pos);
+        return static_cast<size_t>(-1);
+      }
+    }
+    if (n > size - pos - 12 || size - pos - 12 - n < 4) {
+      set_error("%s: truncated record body at offset %zu (len %llu)", path, pos, (unsigned long long)n);
+      return static_cast<size_t>(-1);
+    }
+    out->push_back(RecSpan{pos + 12, static_cast<uint32_t>(n)});
+    pos += 12 + n + 4;
+  }
+  return pos;
+}
+
+namespace {
 
 // Sequential reader for FIFOs / stdin / anything that cannot be mapped
 // (the SageMaker "pipe mode" transport, HVD.py:136).
@@ -326,8 +381,10 @@ int read_float_list(const uint8_t* p, const uint8_t* end, float* out, int cap) {
   return n;
 }
 
+// max_id > 0: every id must lie in [0, max_id) (checked on the 64-bit value, before any narrowing); a violation
+// returns -2 with the offending value in *bad.
 template <typename T>
-int read_int64_list(const uint8_t* p, const uint8_t* end, T* out, int cap) {
+int read_int64_list(const uint8_t* p, const uint8_t* end, T* out, int cap, uint64_t max_id, uint64_t* bad) {
   int n = 0;
   while (p < end) {
     uint64_t tag;
@@ -344,11 +401,13 @@ int read_int64_list(const uint8_t* p, const uint8_t* end, T* out, int cap) {
           return -1;
         }
         if (n >= cap) return -1;
+        if (max_id && v >= max_id) { *bad = v; return -2; }
         out[n++] = static_cast<T>(v);
       }
     } else if (tag == 0x08) {  // unpacked
       uint64_t v;
       if (!get_varint(p, end, v) || n >= cap) return -1;
+      if (max_id && v >= max_id) { *bad = v; return -2; }
       out[n++] = static_cast<T>(v);
     } else if (!skip_field(p, end, tag & 7)) {
       return -1;
@@ -360,7 +419,7 @@ int read_int64_list(const uint8_t* p, const uint8_t* end, T* out, int cap) {
 }  // namespace
 
 int parse_example(const uint8_t* p, uint64_t len, int F, void* ids_out, bool ids_i32, float* vals_out,
-                  float* label_out) {
+                  float* label_out, uint64_t max_id) {
   const uint8_t* end = p + len;
   bool have[3] = {false, false, false};
   while (p < end) {
@@ -429,8 +488,15 @@ int parse_example(const uint8_t* p, uint64_t len, int F, void* ids_out, bool ids
           }
           have[kValues] = true;
         } else if (t4 == 0x1A && key == kIds) {
-          int n = ids_i32 ? read_int64_list<int32_t>(q, le, static_cast<int32_t*>(ids_out), F)
-                          : read_int64_list<int64_t>(q, le, static_cast<int64_t*>(ids_out), F);
+          uint64_t bad = 0;
+          int n = ids_i32 ? read_int64_list<int32_t>(q, le, static_cast<int32_t*>(ids_out), F, max_id, &bad)
+                          : read_int64_list<int64_t>(q, le, static_cast<int64_t*>(ids_out), F, max_id, &bad);
+          if (n == -2) {
+            // what tf.nn.embedding_lookup answers with InvalidArgument on CPU (HVD.py:197,201)
+            set_error("Example: feature id %lld is outside [0, feature_size = %llu)", (long long)bad,
+                      (unsigned long long)max_id);
+            return -1;
+          }
           if (n != F) {
             set_error("Example: key 'ids' holds %d ints, field_size is %d", n, F);
             return -1;

@@ -21,7 +21,7 @@ from .tfrecord import DataError, _lib
 class _Cfg(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "field_size", "batch_size", "num_epochs", "drop_remainder", "shard_n", "shard_i", "num_workers",
-        "num_slots", "ids_i32", "verify_crc", "streaming", "reserved")]
+        "num_slots", "ids_i32", "verify_crc", "streaming", "feature_size")]
 
 
 @dataclass
@@ -57,7 +57,9 @@ class BatchLoader:
     def __init__(self, paths: Sequence[str], field_size: int, batch_size: int, num_epochs: int = 1,
                  drop_remainder: bool = True, shard_n: int = 1, shard_i: int = 0, num_workers: int = 4,
                  num_slots: int = 4, ids_dtype: torch.dtype = torch.int32, verify_crc: bool = True,
-                 streaming: bool = False, pin_memory: Optional[bool] = None):
+                 streaming: bool = False, pin_memory: Optional[bool] = None, feature_size: int = 0):
+        """``feature_size`` > 0: every id must lie in [0, feature_size); a record that violates it ends the stream
+        with a DataError naming the file and byte offset (TF's embedding_lookup raises InvalidArgument there)."""
         lib = _lib()
         if not getattr(lib, "_loader_typed", False):
             lib.dfio_loader_create.restype = C.c_void_p
@@ -78,7 +80,8 @@ class BatchLoader:
             slab, ids, vals, labels = alloc_slab(batch_size, field_size, ids_dtype, pin_memory)
             self._slabs.append(slab); self._ids.append(ids); self._vals.append(vals); self._labels.append(labels)
         cfg = _Cfg(field_size, batch_size, max(1, num_epochs), int(drop_remainder), max(1, shard_n), shard_i,
-                   num_workers, num_slots, int(ids_dtype == torch.int32), int(verify_crc), int(streaming), 0)
+                   num_workers, num_slots, int(ids_dtype == torch.int32), int(verify_crc), int(streaming),
+                   int(feature_size) if 0 < int(feature_size) < 2 ** 31 else 0)
         arr = (C.c_char_p * len(paths))(*[p.encode() for p in paths])
         vp = lambda ts: (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
         self._h = lib.dfio_loader_create(C.byref(cfg), arr, len(paths), vp(self._ids), vp(self._vals), vp(self._labels))

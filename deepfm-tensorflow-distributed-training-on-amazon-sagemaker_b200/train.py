@@ -86,7 +86,7 @@ def make_loader(flags: Flags, files: Sequence[str], batch_size: int, shard, drop
     return BatchLoader(list(files), flags.field_size, batch_size, num_epochs=num_epochs, drop_remainder=drop_remainder,
                        shard_n=shard[0], shard_i=shard[1], num_workers=flags.loader_threads,
                        num_slots=max(2, flags.prefetch_batches), ids_dtype=torch.int32, verify_crc=True,
-                       streaming=streaming)
+                       streaming=streaming, feature_size=flags.feature_size)
 
 
 def equalised_batches(env: DistEnv, flags: Flags, files: Sequence[str], shard) -> Optional[int]:

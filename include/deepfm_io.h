@@ -72,7 +72,8 @@ typedef struct {
   int32_t ids_i32;         /* 1: ids written as int32, else int64 */
   int32_t verify_crc;
   int32_t streaming;       /* 1: paths are FIFOs / stdin, read sequentially without mmap */
-  int32_t reserved;
+  int32_t feature_size;    /* > 0: every id must lie in [0, feature_size); a record that violates it fails the stream
+                              with the file and byte offset (TF's embedding_lookup raises InvalidArgument, HVD.py:197) */
 } dfio_loader_config;
 
 /* slot_*[i] are the caller's buffers for ring slot i:

@@ -236,3 +236,43 @@ def test_loader_delivers_every_record_once_in_order(tmp_path_factory, seed, n, b
         loader.close()
         want = [(int(first_ids[i]), float(labels[i])) for i in range(n) if i % shard_n == shard_i]
         assert got == want
+
+
+def test_loader_rejects_out_of_range_ids(tmp_path):
+    """a too-small --feature_size (or a corrupt record) must fail the batch with file and offset, not reach
+    the embedding tables."""
+    import torch
+    from deepfm_b200.data.loader import BatchLoader
+    from deepfm_b200.data.tfrecord import DataError, generate_synthetic
+    path = str(tmp_path / "tr.tfrecords")
+    generate_synthetic(path, 2000, 39, 5000, n_dense=13, seed=3, pos_rate=0.25, zipf_s=1.05)
+    ok = BatchLoader([path], 39, 100, feature_size=5000, ids_dtype=torch.int32, num_workers=2)
+    assert sum(hb.count for hb in ok) == 2000
+    ok.close()
+    bad = BatchLoader([path], 39, 100, feature_size=1000, ids_dtype=torch.int32, num_workers=2)
+    with pytest.raises(DataError) as ei:
+        for _ in bad:
+            pass
+    assert "outside [0, feature_size = 1000)" in str(ei.value) and "tr.tfrecords" in str(ei.value) and "offset" in str(ei.value)
+    bad.close()
+
+
+def test_parallel_framing_index_matches_sequential_read(tmp_path):
+    """Files larger than one index range (1 MiB) are walked by several threads; the batches must be the records in file
+    order, whatever the shard, batch size or worker count."""
+    import numpy as np
+    import torch
+    from deepfm_b200.data.loader import BatchLoader
+    from deepfm_b200.data import tfrecord as T
+    path = str(tmp_path / "big.tfrecords")
+    n = 12000                                                   # ~3.7 MB: four index ranges
+    T.generate_synthetic(path, n, 39, 117581, n_dense=13, seed=11, pos_rate=0.25, zipf_s=1.05)
+    ref_ids = np.stack([T.parse_example(r, 39)[1] for r in T.iter_records(path)])
+    for workers, batch, shard in ((1, 256, (1, 0)), (7, 100, (1, 0)), (4, 64, (3, 1))):
+        ld = BatchLoader([path], 39, batch, num_epochs=2, drop_remainder=False, shard_n=shard[0], shard_i=shard[1],
+                         num_workers=workers, ids_dtype=torch.int64)
+        got = np.concatenate([hb.feat_ids.numpy().copy() for hb in ld])
+        ld.close()
+        want = ref_ids[shard[1]::shard[0]]
+        assert got.shape[0] == 2 * want.shape[0]
+        assert np.array_equal(got[:want.shape[0]], want) and np.array_equal(got[want.shape[0]:], want)
