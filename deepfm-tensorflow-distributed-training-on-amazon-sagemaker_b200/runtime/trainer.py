@@ -28,6 +28,7 @@ import torch.distributed as dist
 
 from ..data.loader import HostBatch, slab_layout
 from ..models.deepfm import DeepFM, DeepFMConfig
+from ..utils import tracing
 from ..utils.metrics import StreamingAUC
 from ..utils.optimizers import TFOptimizer, canonical_optimizer
 
@@ -161,7 +162,8 @@ class Trainer:
     def checkpoint_tensors(self) -> Dict[str, np.ndarray]:
         if self.backend == "fused":
             torch.cuda.synchronize(self.device)
-        out = {k: v.detach().cpu().numpy().copy() for k, v in self.state_tensors().items()}
+        with tracing.nvtx_range("checkpoint"):
+            out = {k: v.detach().cpu().numpy().copy() for k, v in self.state_tensors().items()}
         if canonical_optimizer(self.opts.optimizer) == "adam":
             # tf.train.AdamOptimizer's non-slot variables: beta^t of the NEXT update (betas are the TF defaults the
             # engine and the eager optimizer are built with)
@@ -306,6 +308,7 @@ class Trainer:
         step's graph, beside the kernels, so no copy and no cross-stream event sits between two graph launches;
         it must stay unchanged until this step has finished.  The loss must be read (``last_loss``) at least
         every other step for its value to be that of the expected step (the graph writes a 2-entry ring)."""
+        tracing.push("train_step")
         if self.backend == "fused":
             if self.uses_graph:
                 self._after_fused_step(self.engine.step_pipelined(host_slab, next_slab))
@@ -316,6 +319,7 @@ class Trainer:
         else:
             ids, vals, labels = self._slab_views(host_slab.to(self.device, non_blocking=True))
             self._eager_step(ids, vals, labels)
+        tracing.pop()
 
     def train_step_device(self, dev_slab: torch.Tensor, next_slab: Optional[torch.Tensor] = None) -> None:
         """Full batch already on the device (same slab layout, same ``next_slab`` contract)."""
@@ -410,9 +414,11 @@ class Trainer:
 
     def evaluate(self, batches: Iterable[HostBatch], auc_mode: str = "tf") -> Dict[str, float]:
         """AUC + mean loss over a stream of batches (model_fn EVAL mode, HVD.py:264-278)."""
+        tracing.push("evaluate")
         auc = StreamingAUC(200, keep_all=auc_mode in ("exact", "both"))
         loss_sum, n = 0.0, 0
         gpu_hist = None
+        dev_pairs = []
         if self.backend == "fused":
             from .engine import auc_histogram
             gpu_hist = torch.zeros(2 * 201, dtype=torch.int64, device=self.device)
@@ -421,9 +427,10 @@ class Trainer:
             loss_sum += ls
             n += hb.count
             if gpu_hist is not None:
-                auc_histogram(prob, hb.labels.to(self.device, non_blocking=True), gpu_hist)
-                if auc.keep_all_enabled:
-                    auc.remember(hb.labels.numpy(), prob.cpu().numpy())
+                lab_d = hb.labels.to(self.device, non_blocking=True)
+                auc_histogram(prob, lab_d, gpu_hist)
+                if auc.keep_all_enabled:               # exact AUC: predictions stay on the device, sorted there
+                    dev_pairs.append((lab_d.clone(), prob.clone()))
             else:
                 auc.update(hb.labels.numpy(), prob.cpu().numpy())
         if gpu_hist is not None:
@@ -440,8 +447,13 @@ class Trainer:
         if auc_mode in ("tf", "both"):
             out["auc"] = auc.result()
         if auc_mode in ("exact", "both"):
-            out["auc_exact"] = auc.result_exact()
+            if dev_pairs:
+                from ..utils.metrics import exact_auc_torch
+                out["auc_exact"] = exact_auc_torch(torch.cat([a for a, _ in dev_pairs]), torch.cat([b for _, b in dev_pairs]))
+            else:
+                out["auc_exact"] = auc.result_exact()
             out.setdefault("auc", out["auc_exact"])
+        tracing.pop()
         return out
 
     def predict(self, batches: Iterable[HostBatch]) -> Iterator[np.ndarray]:

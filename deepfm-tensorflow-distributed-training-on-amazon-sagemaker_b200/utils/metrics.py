@@ -67,6 +67,28 @@ def exact_auc(labels: np.ndarray, preds: np.ndarray) -> float:
     return float((ranks[labels].sum() - n_pos * (n_pos + 1) / 2.0) / (n_pos * n_neg))
 
 
+def exact_auc_torch(labels, preds) -> float:
+    """The same rank statistic computed where the tensors live (the GPU during fused evaluation): a device sort, tie
+    groups by comparing neighbours, average ranks, float64 sums.  Nothing but the final scalar crosses to the host."""
+    import torch
+    preds = preds.reshape(-1).double()
+    pos = labels.reshape(-1) > 0.5
+    n = preds.numel()
+    n_pos = int(pos.sum())
+    n_neg = n - n_pos
+    if n_pos == 0 or n_neg == 0:
+        return float("nan")
+    sp, order = torch.sort(preds, stable=True)
+    new = torch.ones(n, dtype=torch.bool, device=preds.device)
+    new[1:] = sp[1:] != sp[:-1]
+    starts = torch.nonzero(new).reshape(-1)
+    ends = torch.cat([starts[1:], torch.tensor([n], device=preds.device)])
+    avg_rank = 0.5 * (starts + ends - 1).double() + 1.0
+    ranks = avg_rank[torch.cumsum(new.long(), 0) - 1]
+    s = ranks[pos[order]].sum()
+    return float((s - n_pos * (n_pos + 1) / 2.0) / (float(n_pos) * float(n_neg)))
+
+
 class StreamingAUC:
     """Accumulates over batches like the reference's eval_metric_ops (HVD.py:271-278)."""
 

@@ -164,3 +164,13 @@ def test_export_and_serving_signature(tmp_path):
     assert set(got) == {"prob"} and got["prob"].shape == (7,) and got["prob"].dtype == np.float32
     ref = torch.sigmoid(m(torch.from_numpy(ids), torch.from_numpy(vals))).detach().numpy()
     np.testing.assert_allclose(got["prob"], ref, rtol=1e-6)
+
+
+def test_exact_auc_torch_matches_numpy_with_ties():
+    import numpy as np
+    import torch
+    from deepfm_b200.utils.metrics import exact_auc, exact_auc_torch
+    rng = np.random.default_rng(0)
+    preds = np.round(rng.random(5000), 2).astype(np.float32)        # many ties
+    labels = (rng.random(5000) < 0.3).astype(np.float32)
+    assert abs(exact_auc_torch(torch.from_numpy(labels), torch.from_numpy(preds)) - exact_auc(labels, preds)) < 1e-12

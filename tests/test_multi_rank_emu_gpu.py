@@ -162,3 +162,16 @@ def test_many_steps_keep_replicas_identical():
     _assert_replicas_identical(emu)
     assert last < first
     emu.close()
+
+
+def test_watchdog_trips_when_a_rank_is_out_of_step():
+    """A rank that waits for a peer's flag longer than DFM_COMM_TIMEOUT_S prints what it waits for and traps -- in a
+    subprocess, because a trap leaves the CUDA context unusable."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, os.path.join(root, "scripts", "gpu_watchdog_trip.py")], capture_output=True,
+                       text=True, timeout=180)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "[dfm comm watchdog]" in p.stdout + p.stderr and "watchdog fired" in p.stdout
