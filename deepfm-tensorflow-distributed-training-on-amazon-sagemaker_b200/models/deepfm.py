@@ -119,6 +119,10 @@ class DeepFM(nn.Module):
             mean, var = mean_b, var_b
         return (x - mean) * torch.rsqrt(var + BN_EPS) * self.bn_gamma[i] + self.bn_beta[i]
 
+    # Optional: a callable (layer, rows, cols) -> bool keep mask that replaces torch's dropout stream in training --
+    # used to give this oracle the fused engine's Philox masks (utils/philox.py) so the two differ by rounding only.
+    dropout_mask_fn = None
+
     def forward(self, feat_ids: torch.Tensor, feat_vals: torch.Tensor, training: bool = False) -> torch.Tensor:
         """Returns logits [B]; ``prob = sigmoid(logits)`` (HVD.py:249)."""
         cfg = self.cfg
@@ -146,7 +150,10 @@ class DeepFM(nn.Module):
             if cfg.batch_norm:
                 h = self._bn(h, i, training)
             if training and cfg.dropout_keep[i] < 1.0:
-                h = F.dropout(h, p=1.0 - cfg.dropout_keep[i], training=True)
+                if self.dropout_mask_fn is not None:
+                    h = h * self.dropout_mask_fn(i, h.shape[0], h.shape[1]).to(h.dtype) / cfg.dropout_keep[i]
+                else:
+                    h = F.dropout(h, p=1.0 - cfg.dropout_keep[i], training=True)
         y_d = (h @ self.out_w).view(-1) + self.out_b
         return self.fm_bias + y_w + y_v + y_d
 

@@ -26,26 +26,41 @@ for name, part in (("tr", recs[:cut]), ("va", recs[cut:])):
         for r in part:
             w.write(r)
 B, EPOCHS = 256, int(os.environ.get("DFM_AUC_EPOCHS", "3"))
+SEEDS = [int(x) for x in os.environ.get("DFM_AUC_SEEDS", "1,2,3").split(",")]
+MODE = os.environ.get("DFM_AUC_TABLE_MODE", "lazy")
 cfg = DeepFMConfig(39, 117581, 32, (256, 128, 64), (0.5, 0.5, 0.5), l2_reg=1e-4)
-init = DeepFM(cfg, seed=1)
-out = {"records": len(recs), "train": cut, "batch": B, "epochs": EPOCHS}
+out = {"records": len(recs), "train": cut, "batch": B, "epochs": EPOCHS, "seeds": SEEDS, "table_update_mode": MODE,
+       "dropout": "the eager arm uses the fused engine's Philox keep masks (same seed, step, layer, row, column)", "runs": []}
 backends = ["eager"] + (["fused"] if torch.cuda.is_available() else [])
-for backend in backends:
-    dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
-    tr = Trainer(cfg, TrainerOptions(batch_size=B, optimizer="Adam", learning_rate=5e-4, backend=backend, seed=1),
-                 device=dev, init_model=copy.deepcopy(init))   # the eager trainer trains the module it is given
-    t0 = time.time()
-    for _ in range(EPOCHS):
-        loader = BatchLoader([paths["tr"]], 39, B, num_epochs=1, drop_remainder=True, num_workers=2, num_slots=6)
-        for _hb in tr.train_batches(loader):
-            pass
+for seed in SEEDS:
+    init = DeepFM(cfg, seed=seed)
+    run = {"seed": seed}
+    for backend in backends:
+        dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
+        tr = Trainer(cfg, TrainerOptions(batch_size=B, optimizer="Adam", learning_rate=5e-4, backend=backend, seed=seed,
+                                         table_update_mode=MODE, dropout_stream="engine"),
+                     device=dev, init_model=copy.deepcopy(init))   # the eager trainer trains the module it is given
+        t0 = time.time()
+        for _ in range(EPOCHS):
+            loader = BatchLoader([paths["tr"]], 39, B, num_epochs=1, drop_remainder=True, num_workers=2, num_slots=6)
+            for _hb in tr.train_batches(loader):
+                pass
+            loader.close()
+        loader = BatchLoader([paths["va"]], 39, B, num_epochs=1, drop_remainder=False, num_workers=2)
+        ev = tr.evaluate(loader, auc_mode="both")
         loader.close()
-    loader = BatchLoader([paths["va"]], 39, B, num_epochs=1, drop_remainder=False, num_workers=2)
-    ev = tr.evaluate(loader, auc_mode="both")
-    loader.close()
-    out[backend] = {"auc": round(ev["auc"], 5), "auc_exact": round(ev.get("auc_exact", float("nan")), 5),
-                    "loss": round(ev["data_loss"], 5), "train_s": round(time.time() - t0, 2), "device": str(dev)}
-    tr.close()
-if "fused" in out:
-    out["auc_diff"] = round(abs(out["fused"]["auc"] - out["eager"]["auc"]), 5)
+        run[backend] = {"auc": round(ev["auc"], 5), "auc_exact": round(ev.get("auc_exact", float("nan")), 5),
+                        "loss": round(ev["data_loss"], 5), "train_s": round(time.time() - t0, 2)}
+        tr.close()
+    if "fused" in run:
+        run["auc_diff"] = round(run["fused"]["auc"] - run["eager"]["auc"], 5)
+    out["runs"].append(run)
+if "fused" in backends:
+    d = [r["auc_diff"] for r in out["runs"]]
+    out["auc_diff_mean"] = round(sum(d) / len(d), 5)
+    out["auc_diff_max_abs"] = round(max(abs(x) for x in d), 5)
+for b in backends:
+    a = [r[b]["auc"] for r in out["runs"]]
+    out[f"{b}_auc_mean"] = round(sum(a) / len(a), 5)
+    out[f"{b}_auc_spread"] = round(max(a) - min(a), 5)
 print(json.dumps(out))

@@ -396,3 +396,25 @@ def test_square_loss_without_batch_norm():
     for name in ("Deep-part/mlp0/weights", "Deep-part/deep_out/weights", "fm_bias"):
         assert _rel(before[name] - eng.variables()[name], dict(m.tf_variables())[name].grad) < 2e-2, name
     eng.close()
+
+
+def test_python_philox_reproduces_the_engine_dropout_masks():
+    """utils/philox.keep_mask == the keep decisions the layer kernels make (same seed, step, layer, row, column)."""
+    from deepfm_b200.utils.philox import keep_mask
+    cfg, m, eng, ids, vals, labels = _setup(300, [256, 128, 64], keep=[0.5, 0.8, 0.3], opt="GD", lr=0.0)
+    ids32 = ids.int().contiguous()
+    eng.forward(ids32, vals, labels)
+    evals = [eng.buffer("act", l + 1, "bf16").clone() for l in range(3)]
+    eng.train_step(ids32, vals, labels)                      # optimizer step 1, seed 7 (see _setup)
+    torch.cuda.synchronize()
+    for l, (n, keep) in enumerate(zip([256, 128, 64], [0.5, 0.8, 0.3])):
+        pitch = (n + 1 + 15) // 16 * 16
+        h = eng.buffer("act", l + 1, "bf16").view(-1, pitch)[:300, :n].float()
+        mask = keep_mask(7, 1, l, 300, n, keep, device="cuda")
+        assert abs(mask.float().mean().item() - keep) < 0.02
+        assert (h[~mask] == 0).all()                          # dropped where the mirror says so
+        if l == 0:                                            # layer 0's input does not depend on earlier masks
+            he = evals[0].view(-1, pitch)[:300, :n].float()
+            live = he > 0
+            assert ((h > 0) == (live & mask)).all()
+    eng.close()
