@@ -222,11 +222,12 @@ class Trainer:
             if hb.count == self.opts.batch_size and self.uses_graph and hb.slab is not None and hb.slab.is_pinned():
                 self.train_step_host(hb.slab)
                 return
-            ids = hb.feat_ids.to(self.device, non_blocking=True)
+            # blocking copies: the batch may be a view of a loader ring slot that is recycled as soon as we return
+            ids = hb.feat_ids.to(self.device)
             if ids.dtype != torch.int32:
                 ids = ids.int()
-            vals = hb.feat_vals.to(self.device, non_blocking=True)
-            labels = hb.labels.to(self.device, non_blocking=True)
+            vals = hb.feat_vals.to(self.device)
+            labels = hb.labels.to(self.device)
             self.engine.train_step(ids.contiguous(), vals.contiguous(), labels.contiguous())
             self._after_fused_step(count=hb.count)
             if self.uses_graph and hb.count != self.opts.batch_size:
@@ -261,6 +262,16 @@ class Trainer:
                 loader.release(slot)
 
         done = 0
+        if not deferred:
+            # No look-ahead here: asking the loader for the next batch gives the current batch's ring slot back to the
+            # parser threads, so a batch must be consumed (copied to the device, synchronously) before the next is fetched.
+            for hb in it:
+                if limit is not None and done >= limit:
+                    break
+                self.train_batch(hb)
+                done += 1
+                yield hb
+            return
         if deferred:
             loader.defer_release = True
             self.engine.reset_pipeline()
@@ -434,7 +445,7 @@ class Trainer:
             loss_sum += ls
             n += hb.count
             if gpu_hist is not None:
-                lab_d = hb.labels.to(self.device, non_blocking=True)
+                lab_d = hb.labels.to(self.device)        # blocking: the ring slot is recycled at the next fetch
                 auc_histogram(prob, lab_d, gpu_hist)
                 if auc.keep_all_enabled:               # exact AUC: predictions stay on the device, sorted there
                     dev_pairs.append((lab_d.clone(), prob.clone()))

@@ -28,8 +28,12 @@ for name, part in (("tr", recs[:cut]), ("va", recs[cut:])):
 B, EPOCHS = 256, int(os.environ.get("DFM_AUC_EPOCHS", "3"))
 SEEDS = [int(x) for x in os.environ.get("DFM_AUC_SEEDS", "1,2,3").split(",")]
 MODE = os.environ.get("DFM_AUC_TABLE_MODE", "lazy")
-cfg = DeepFMConfig(39, 117581, 32, (256, 128, 64), (0.5, 0.5, 0.5), l2_reg=1e-4)
-out = {"records": len(recs), "train": cut, "batch": B, "epochs": EPOCHS, "seeds": SEEDS, "table_update_mode": MODE,
+KEEP = float(os.environ.get("DFM_AUC_KEEP", "0.5"))
+OPT = os.environ.get("DFM_AUC_OPT", "Adam")
+LR = float(os.environ.get("DFM_AUC_LR", "5e-4"))
+GRAPH = os.environ.get("DFM_AUC_GRAPH", "1") != "0"
+cfg = DeepFMConfig(39, 117581, 32, (256, 128, 64), (KEEP, KEEP, KEEP), l2_reg=float(os.environ.get("DFM_AUC_L2", "1e-4")))
+out = {"keep": KEEP, "opt": OPT, "lr": LR, "graph": GRAPH,"records": len(recs), "train": cut, "batch": B, "epochs": EPOCHS, "seeds": SEEDS, "table_update_mode": MODE,
        "dropout": "the eager arm uses the fused engine's Philox keep masks (same seed, step, layer, row, column)", "runs": []}
 backends = ["eager"] + (["fused"] if torch.cuda.is_available() else [])
 for seed in SEEDS:
@@ -37,8 +41,8 @@ for seed in SEEDS:
     run = {"seed": seed}
     for backend in backends:
         dev = torch.device("cuda", 0) if torch.cuda.is_available() else torch.device("cpu")
-        tr = Trainer(cfg, TrainerOptions(batch_size=B, optimizer="Adam", learning_rate=5e-4, backend=backend, seed=seed,
-                                         table_update_mode=MODE, dropout_stream="engine"),
+        tr = Trainer(cfg, TrainerOptions(batch_size=B, optimizer=OPT, learning_rate=LR, backend=backend, seed=seed,
+                                         table_update_mode=MODE, dropout_stream="engine", cuda_graph=GRAPH),
                      device=dev, init_model=copy.deepcopy(init))   # the eager trainer trains the module it is given
         t0 = time.time()
         for _ in range(EPOCHS):

@@ -161,3 +161,38 @@ def test_sync_dp_equals_big_batch_with_scaled_lr(tmp_path, opt):
         single.train_batch(hb)
     for k, v in single.variables().items():
         torch.testing.assert_close(r0[k], v.detach(), rtol=2e-4, atol=2e-6)
+
+
+def test_train_batches_consumes_every_batch_once_in_order(tmp_path):
+    """Regression: without the pipelined path a look-ahead fetch used to hand the current batch's ring slot back to the
+    parser threads before it was trained on (batches skipped / seen twice).  With frozen weights the per-step loss is
+    a fingerprint of the batch: it must equal the loss of the file's batches in file order."""
+    import numpy as np
+    import torch
+    from deepfm_b200.data import tfrecord as T
+    from deepfm_b200.data.loader import BatchLoader, HostBatch
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.runtime.trainer import Trainer, TrainerOptions
+    path = str(tmp_path / "tr.tfrecords")
+    B, n = 32, 32 * 40
+    T.generate_synthetic(path, n, 39, 5000, n_dense=13, seed=7)
+    cfg = DeepFMConfig(39, 5000, 8, (16, 8), (1.0, 1.0), l2_reg=0.0)
+    init = DeepFM(cfg, seed=1)
+    with torch.no_grad():
+        init.fm_v.mul_(50); init.fm_w.mul_(50)
+    tr = Trainer(cfg, TrainerOptions(batch_size=B, optimizer="GD", learning_rate=0.0, backend="eager", seed=1),
+                 device="cpu", init_model=init)
+    loader = BatchLoader([path], 39, B, num_epochs=1, drop_remainder=True, num_workers=3, num_slots=3)
+    got = []
+    for _ in tr.train_batches(loader):
+        got.append(tr.last_loss(wait_current=True))
+    loader.close()
+    recs = [T.parse_example(r, 39) for r in T.iter_records(path)]
+    want = []
+    for b in range(n // B):
+        part = recs[b * B:(b + 1) * B]
+        ids = torch.from_numpy(np.stack([p[1] for p in part])); vals = torch.from_numpy(np.stack([p[2] for p in part]))
+        labels = torch.tensor([p[0] for p in part])
+        with torch.no_grad():
+            want.append(float(init.data_loss(init(ids, vals), labels)))
+    np.testing.assert_allclose(got, want, rtol=1e-5)
