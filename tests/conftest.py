@@ -37,4 +37,11 @@ def val_tfrecords():
     local = os.path.join(ROOT, "tests", "data", "val_sample.tfrecords")
     if os.path.exists(local):
         return local
-    pytest.skip("no TFRecord sample available")
+    # the GPU box has neither: a Criteo-shaped synthetic file of the same size written by the framework's own generator
+    import tempfile
+    from deepfm_b200.data.tfrecord import generate_synthetic
+    path = os.path.join(tempfile.gettempdir(), "dfm_val_standin_10000.tfrecords")
+    if not os.path.exists(path):
+        generate_synthetic(path + ".tmp", 10000, 39, 117581, n_dense=13, seed=2553, pos_rate=0.2553, zipf_s=1.05)
+        os.replace(path + ".tmp", path)
+    return path

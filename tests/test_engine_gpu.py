@@ -248,7 +248,9 @@ def test_training_on_the_bundled_data_reaches_the_eager_auc(tmp_path, val_tfreco
     init = DeepFM(cfg, seed=1)
     aucs = {}
     for backend in ("eager", "fused"):
-        tr = Trainer(cfg, TrainerOptions(batch_size=256, optimizer="Adam", learning_rate=5e-4, backend=backend, seed=1),
+        # both arms use the engine's Philox dropout masks, so they differ by bf16 rounding and summation order only
+        tr = Trainer(cfg, TrainerOptions(batch_size=256, optimizer="Adam", learning_rate=5e-4, backend=backend, seed=1,
+                                         dropout_stream="engine"),
                      device=torch.device("cuda", 0), init_model=copy.deepcopy(init))
         for _ in range(3):
             loader = BatchLoader([paths["tr"]], 39, 256, num_epochs=1, drop_remainder=True, num_workers=2, num_slots=6)
@@ -260,7 +262,8 @@ def test_training_on_the_bundled_data_reaches_the_eager_auc(tmp_path, val_tfreco
         loader.close()
         tr.close()
     assert aucs["eager"]["auc"] > 0.68 and aucs["fused"]["auc"] > 0.68, aucs
-    assert abs(aucs["eager"]["auc"] - aucs["fused"]["auc"]) < 0.02, aucs
+    # measured with shared masks: |diff| <= 0.0011 over three seeds (profiles/auc_parity_synthetic_r2.json)
+    assert abs(aucs["eager"]["auc"] - aucs["fused"]["auc"]) < 0.005, aucs
     assert abs(aucs["fused"]["auc"] - aucs["fused"]["auc_exact"]) < 0.01, aucs
 
 
