@@ -52,8 +52,9 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5000)
     ap.add_argument("--warmup", type=int, default=100)
-    ap.add_argument("--config", default="criteo", choices=sorted(CONFIGS),
-                    help="criteo = BASELINE.json config 2 (the headline); large = config 3 (33M-row table, emb 64, MLP 400x3)")
+    ap.add_argument("--config", default="criteo", choices=sorted(CONFIGS) + ["sweep"],
+                    help="criteo = BASELINE.json config 2 (the headline); large = config 3 (33M-row table, emb 64, MLP 400x3); "
+                         "sweep = config 5: fused collectives vs NCCL, dense 4 KB-256 MB and sparse 1K-1M ids (needs --gpus >= 2)")
     ap.add_argument("--impl", default="fused", choices=["fused", "reference", "eager"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--pool", type=int, default=POOL)
@@ -176,9 +177,37 @@ def make_host_pool(batch: int, pool: int, rank: int, world: int):
     return slabs, n / max(parse_s, 1e-9)
 
 
+def run_sweep(args):
+    """BASELINE.json config 5: gradient collective sweep, fused NVLink kernels vs torch.distributed (NCCL)."""
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    import torch
+    import torch.distributed as dist
+    world, rank, local_rank = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+    if world < 2:
+        raise SystemExit("--config sweep needs a torchrun launch with >= 2 ranks")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev)
+    from deepfm_b200.parallel.collectives import sweep_dense, sweep_sparse
+    dense = sweep_dense(dev, [1 << k for k in range(12, 29)])                     # 4 KB .. 256 MB
+    sparse = sweep_sparse(dev, [1_000, 4_000, 16_000, 64_000, 256_000, 1_000_000])
+    out = {"metric": "collective_sweep", "n_gpus": world, "impl": "fused vs nccl", "unit": "us (device, max over ranks)",
+           "dense_allreduce": dense, "sparse_exchange_update": sparse}
+    dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    return 0
+
+
 def main():
     global FEATURE, EMB, LAYERS
     args = parse_args()
+    if args.config == "sweep":
+        return run_sweep(args)
     FEATURE, EMB, LAYERS = CONFIGS[args.config]["feature"], CONFIGS[args.config]["emb"], CONFIGS[args.config]["layers"]
     if args.impl == "reference":
         print(json.dumps({"impl": "reference", "unavailable":

@@ -480,6 +480,59 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
   if (threadIdx.x == 0) kstamp_any(a.st, kStampSparseEnd);
 }
 
+// =================================================================================================
+// stand-alone all-reduce over a symmetric buffer (the dense half of the step without the optimizer; used by the
+// collective sweep of bench.py and available to callers that keep other tensors in symmetric memory)
+// =================================================================================================
+// buf[r]: rank r's copy of n floats (n % 4 == 0); flags: 2 arrays [world][kCommMaxCtas] per rank behind the data.
+// Sum lands in every copy.  Same protocol as dense_sync_kernel: barrier, rank r reduces chunk r and publishes it,
+// barrier.  `epoch` must increase by one per call (kept by the caller on the host: this kernel is not graph-replayed).
+struct AllReduceArgs {
+  float* buf[kCommMaxRanks];
+  float* mc;                       // multicast alias of the copies or null
+  unsigned int* flags[kCommMaxRanks];
+  int world, rank, ctas;
+  long long n4;                    // float4 groups
+  unsigned int epoch;
+  long long watchdog;
+};
+
+__global__ void __launch_bounds__(kXThreads, 1)
+allreduce_kernel(const __grid_constant__ AllReduceArgs a) {
+  const int N = a.world, cta = blockIdx.x;
+  auto barrier = [&](int which) {
+    __syncthreads();
+    if (threadIdx.x < N)
+      st_release_sys(a.flags[threadIdx.x] + size_t(which * N + a.rank) * kCommMaxCtas + cta, a.epoch);
+    if (threadIdx.x < N) {
+      const unsigned int* mine = a.flags[a.rank] + size_t(which * N + threadIdx.x) * kCommMaxCtas + cta;
+      const long long t0 = clock64();
+      while (ld_relaxed_sys(mine) < a.epoch)
+        if (clock64() - t0 > a.watchdog) comm_watchdog_trip(a.rank, cta, 2, threadIdx.x, a.epoch);
+      (void)ld_acquire_sys(mine);
+    }
+    __syncthreads();
+  };
+  const long long c4 = (a.n4 + N - 1) / N;              // groups per rank chunk
+  const long long per = (c4 + a.ctas - 1) / a.ctas;     // groups per CTA sub-slice
+  barrier(0);                                           // every rank's input is in place
+  const long long lo = a.rank * c4 + cta * per, hi = min(min(lo + per, (a.rank + 1) * c4), a.n4);
+  for (long long g = lo + threadIdx.x; g < hi; g += blockDim.x) {
+    if (a.mc) {
+      const float4 s = multimem_ld_reduce_f4(a.mc + 4 * g);
+      multimem_st_f4(a.mc + 4 * g, s);
+    } else {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int q = 0; q < N; ++q) {
+        const float4 v = ld_volatile_f4(a.buf[q] + 4 * g);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      for (int q = 0; q < N; ++q) st_volatile_f4(a.buf[q] + 4 * g, acc);
+    }
+  }
+  barrier(1);                                           // every chunk has been published everywhere
+}
+
 // ------------------------------------------------------------------------------------------------
 template <typename K>
 static int launch_collective(K real_kernel, K emu_kernel, int ctas, const XchgArgs& x, const XchgArgs* emu,
@@ -506,3 +559,27 @@ int launch_exchange_apply(const XchgArgs& x, const XchgArgs* emu, int emu_ranks,
 }
 
 }  // namespace dfm
+
+using namespace dfm;
+
+// data_ptrs / flag_ptrs: `world` device pointers each (peer-mapped); flags = 2 * world * 160 zero-initialised uint32 per
+// rank; epoch: 1, 2, 3, ... per call on every rank.
+extern "C" int dfm_allreduce_f32(int world, int rank, void* const* data_ptrs, void* data_mc, void* const* flag_ptrs,
+                                 long long n, unsigned int epoch, dfm_stream_t stream) {
+  DFM_REQUIRE(world >= 2 && world <= kCommMaxRanks && rank >= 0 && rank < world, "dfm_allreduce_f32: world %d rank %d", world, rank);
+  DFM_REQUIRE(n > 0 && n % 4 == 0 && epoch > 0, "dfm_allreduce_f32: n must be a positive multiple of 4, epoch >= 1");
+  AllReduceArgs a{};
+  for (int r = 0; r < world; ++r) {
+    a.buf[r] = static_cast<float*>(data_ptrs[r]);
+    a.flags[r] = static_cast<unsigned int*>(flag_ptrs[r]);
+  }
+  a.mc = static_cast<float*>(data_mc);
+  a.world = world; a.rank = rank; a.n4 = n / 4; a.epoch = epoch;
+  // latency-bound below ~1 MB: few CTAs keep the barrier cheap; bandwidth-bound above: every SM moves data
+  const long long per_rank = a.n4 / world;
+  a.ctas = int(std::max<long long>(1, std::min<long long>(kCommMaxCtas - 12, (per_rank + kXThreads - 1) / kXThreads)));
+  a.watchdog = (long long)(120.0 * 1.9e9);
+  allreduce_kernel<<<a.ctas, kXThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}

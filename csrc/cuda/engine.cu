@@ -934,3 +934,42 @@ extern "C" int dfm_ipc_open(const void* handle, void** ptr) {
   *ptr = p;
   return DFM_OK;
 }
+
+// ---- the sparse exchange on its own (collective sweep / profiling) ---------------------------
+namespace dfm {
+__global__ void open_exchange_kernel(StepState* st, int n) {
+  st->count = n;                 // dedupe walks count * F positions (F = 1 here)
+  st->step += 1;
+  st->comm_epoch += 1;
+  open_step_consts(st);
+  for (int o = 0; o < 8; ++o) st->n_seg[o] = 0;
+}
+__global__ void fill_segments_kernel(const StepState* st, float* G, int cap, int gp, int Ke, int world) {
+  for (int o = 0; o < world; ++o)
+    for (long long i = blockIdx.x * blockDim.x + threadIdx.x; i < (long long)st->n_seg[o] * (Ke + 1); i += (long long)gridDim.x * blockDim.x) {
+      const long long s = i / (Ke + 1);
+      G[(size_t(o) * cap + s) * gp + (i - s * (Ke + 1))] = 1.f;
+    }
+}
+}  // namespace dfm
+
+extern "C" int dfm_engine_exchange_prepare(void* h, const int* ids, int n, dfm_stream_t s_) {
+  Engine* E = static_cast<Engine*>(h);
+  cudaStream_t s = static_cast<cudaStream_t>(s_);
+  DFM_REQUIRE(E->comm_ready && !E->emu, "dfm_engine_exchange_prepare: attach the multi-GPU views first");
+  const int cap = E->cfg.batch_max * E->cfg.field_size;
+  DFM_REQUIRE(ids && n > 0 && n <= cap, "dfm_engine_exchange_prepare: n %d outside (0, %d]", n, cap);
+  open_exchange_kernel<<<1, 1, 0, s>>>(E->st, n);
+  DFM_LAUNCH_CHECK();
+  int rc = launch_dedupe(ids, 1, E->st, E->slot_of, E->uniq_ids, n, E->xa.cv.world, cap, E->cfg.feature_size, s);
+  if (rc) return rc;
+  fill_segments_kernel<<<296, 256, 0, s>>>(E->st, E->G, cap, g_pitch(E->cfg.embedding_size), E->cfg.embedding_size, E->xa.cv.world);
+  DFM_LAUNCH_CHECK();
+  return DFM_OK;
+}
+
+extern "C" int dfm_engine_exchange_run(void* h, dfm_stream_t s_) {
+  Engine* E = static_cast<Engine*>(h);
+  DFM_REQUIRE(E->comm_ready && !E->emu, "dfm_engine_exchange_run: attach the multi-GPU views first");
+  return launch_exchange_apply(E->xa, nullptr, 0, static_cast<cudaStream_t>(s_));
+}

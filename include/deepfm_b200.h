@@ -158,6 +158,17 @@ int dfm_engine_comm_multicast(void* engine);
  * all virtual ranks (separate launches that wait on one another on one GPU are not guaranteed to co-run). */
 int dfm_engine_emu_attach(void* const* engines, int n, void* const* grad_tables);
 int dfm_engine_emu_collectives(void* const* engines, int n, dfm_stream_t stream);
+/* Stand-alone sum all-reduce of n fp32 values (n % 4 == 0) held in symmetric memory, in place in every rank's copy:
+ * the dense half of the step without the optimizer (ncclAllReduce's role in Horovod's fusion buffer, HVD.py:296).
+ * data_ptrs / flag_ptrs: `world` peer-mapped pointers each; data_mc: NVLS multicast alias of the copies or NULL;
+ * flags: 2 * world * 160 zero-initialised uint32 per rank; epoch = 1, 2, 3, ... per call, the same on every rank. */
+int dfm_allreduce_f32(int world, int rank, void* const* data_ptrs, void* data_mc, void* const* flag_ptrs,
+                      long long n, unsigned int epoch, dfm_stream_t stream);
+/* The sparse exchange + owner-sharded lazy update of a multi-GPU engine on its own (collective sweep, profiling):
+ * prepare de-duplicates `n` ids (n <= batch_max * field_size) and gives every distinct id a gradient row of ones;
+ * run launches the exchange kernel for them.  Both are collective: every rank calls them the same number of times. */
+int dfm_engine_exchange_prepare(void* engine, const int* ids, int n, dfm_stream_t stream);
+int dfm_engine_exchange_run(void* engine, dfm_stream_t stream);
 /* Plain device allocations with CUDA IPC export / import (the fallback symmetric-memory provider). */
 int dfm_dev_alloc(long long bytes, void** ptr);            /* cudaMalloc + zero fill */
 int dfm_dev_free(void* ptr);
