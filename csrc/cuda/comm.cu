@@ -159,6 +159,7 @@ dense_sync_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __restric
   __shared__ XchgArgs sx;
   int cta;
   const XchgArgs& x = select_args<kEmu>(pa, emu, &sx, true, cta);
+  pdl_wait();                                          // launched behind the weight-gradient GEMM
   const CommView& cv = x.cv;
   const DenseArgs& d = x.d;
   const OptStepConsts c = make_opt_consts(x.hyper, x.a.st);
@@ -256,6 +257,7 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
   __shared__ XchgArgs sx;
   int cta;
   const XchgArgs& x = select_args<kEmu>(pa, emu, &sx, false, cta);
+  pdl_wait();                                          // launched behind embed_bwd
   const CommView& cv = x.cv;
   const SparseArgs& a = x.a;
   const OptHyper& hyper = x.hyper;
@@ -517,10 +519,16 @@ allreduce_kernel(const __grid_constant__ AllReduceArgs a) {
   const long long per = (c4 + a.ctas - 1) / a.ctas;     // groups per CTA sub-slice
   barrier(0);                                           // every rank's input is in place
   const long long lo = a.rank * c4 + cta * per, hi = min(min(lo + per, (a.rank + 1) * c4), a.n4);
-  for (long long g = lo + threadIdx.x; g < hi; g += blockDim.x) {
+  constexpr int kU = 4;                                 // independent groups in flight per thread (bandwidth-bound sizes)
+  for (long long g = lo + threadIdx.x; g < hi; g += (long long)blockDim.x * (a.mc ? kU : 1)) {
     if (a.mc) {
-      const float4 s = multimem_ld_reduce_f4(a.mc + 4 * g);
-      multimem_st_f4(a.mc + 4 * g, s);
+      float4 s[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (g + (long long)u * blockDim.x < hi) s[u] = multimem_ld_reduce_f4(a.mc + 4 * (g + (long long)u * blockDim.x));
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+        if (g + (long long)u * blockDim.x < hi) multimem_st_f4(a.mc + 4 * (g + (long long)u * blockDim.x), s[u]);
     } else {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int q = 0; q < N; ++q) {
@@ -538,7 +546,10 @@ template <typename K>
 static int launch_collective(K real_kernel, K emu_kernel, int ctas, const XchgArgs& x, const XchgArgs* emu,
                              int emu_ranks, cudaStream_t stream) {
   if (emu_ranks <= 0) {
-    real_kernel<<<ctas, kXThreads, 0, stream>>>(x, nullptr);
+    // programmatic dependent launch: the grid is scheduled while its predecessor in the stream drains, and waits
+    // (griddepcontrol.wait) before it reads anything that kernel wrote
+    const XchgArgs* none = nullptr;
+    DFM_CUDA_CHECK(launch_pdl(kPdlSparse, real_kernel, dim3(ctas), dim3(kXThreads), 0, stream, x, none));
   } else {
     // all virtual ranks' CTAs wait on one another: a cooperative launch guarantees (or refuses) co-residency
     const XchgArgs* ep = emu;
