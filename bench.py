@@ -190,10 +190,16 @@ def run_eager_graph(args):
     import torch
     import torch.distributed as dist
     world, rank, local_rank = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
+    if world > 1:
+        # the NCCL all-reduce captured inside the step graph did not complete on this box (the run sat in the first replay
+        # until it was killed), so this arm is single-GPU; the op-by-op `eager` arm is the multi-GPU stock baseline
+        os.dup2(real_stdout, 1)
+        if rank == 0:
+            print(json.dumps({"impl": "eager_graph", "unavailable": "single-GPU only: NCCL all-reduce inside the captured "
+                              "step hung here; use --impl eager for N > 1"}), flush=True)
+        return 0
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
     from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
     cfg = DeepFMConfig(field_size=FIELD, feature_size=FEATURE, embedding_size=EMB, deep_layers=LAYERS, dropout_keep=KEEP, l2_reg=L2)
     model = DeepFM(cfg, seed=1).to(dev)

@@ -178,13 +178,17 @@ dense_sync_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __restric
   // per-CTA flags only cover what the same-numbered CTA wrote)
   for (int q = 0; q < N; ++q) {
     const int lo = q * c4 + cta * per2, hi = min(min(lo + per2, (q + 1) * c4), n4);
-    for (int gq = lo + threadIdx.x; gq < hi; gq += blockDim.x) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int gq = lo + threadIdx.x; gq < hi; gq += 2 * blockDim.x) {
+      const int g1 = min(gq + int(blockDim.x), hi - 1);       // second group of the pair (clamped: a harmless repeat)
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc;
       for (int k = 0; k < d.ksplit; ++k) {
         const float4 v = *reinterpret_cast<const float4*>(d.part + size_t(k) * d.part_stride + 4 * size_t(gq));
+        const float4 w = *reinterpret_cast<const float4*>(d.part + size_t(k) * d.part_stride + 4 * size_t(g1));
         acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        acc1.x += w.x; acc1.y += w.y; acc1.z += w.z; acc1.w += w.w;
       }
       *reinterpret_cast<float4*>(my_dP + 4 * size_t(gq)) = acc;
+      *reinterpret_cast<float4*>(my_dP + 4 * size_t(g1)) = acc1;
     }
   }
   stamp(cv, cta, 12);
@@ -217,26 +221,67 @@ dense_sync_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __restric
   cta_wait_all_ranks(cv, cta, 1, epoch);
   stamp(cv, cta, 10);
 
-  // phase 2: the sums of my namesake CTAs' sub-slices (one per chunk) have landed in my copy
+  // phase 2: the sums of my namesake CTAs' sub-slices (one per chunk) have landed in my copy.  Two float4 groups per
+  // thread in flight (the loop is a chain of dependent loads), parameters and slots moved as float4.
+  auto apply_group = [&](int gq, const float4& sum, float4& p4, float4& m4, float4& v4) {
+    float* pp = &p4.x; float* mm = &m4.x; float* vv = &v4.x;
+    const float gr[4] = {sum.x * inv_n, sum.y * inv_n, sum.z * inv_n, sum.w * inv_n};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int i = 4 * gq + j;
+      if (i >= n_red) break;
+      opt_apply(c, gr[j], pp[j], mm[j], vv[j]);
+      if (i == d.n - 2) {                              // fm_bias shares b_out's gradient
+        float p2 = d.P[d.n - 1], m2 = d.s0[d.n - 1], v2 = d.s1[d.n - 1];
+        opt_apply(c, gr[j], p2, m2, v2);
+        d.P[d.n - 1] = p2; d.s0[d.n - 1] = m2; d.s1[d.n - 1] = v2;
+      }
+    }
+  };
+  auto store_group = [&](int gq, const float4& p4, const float4& m4, const float4& v4) {
+    const int i0 = 4 * gq;
+    if (i0 + 4 <= n_red) {
+      *reinterpret_cast<float4*>(d.P + i0) = p4;
+      *reinterpret_cast<float4*>(d.s0 + i0) = m4;
+      *reinterpret_cast<float4*>(d.s1 + i0) = v4;
+      if (i0 + 4 <= d.wb_skip_lo || i0 >= d.wb_skip_hi) {
+        *reinterpret_cast<uint2*>(d.Wb + i0) = make_uint2(pack_bf16x2(p4.x, p4.y), pack_bf16x2(p4.z, p4.w));
+        return;
+      }
+    }
+    const float* pp = &p4.x; const float* mm = &m4.x; const float* vv = &v4.x;
+    for (int j = 0; j < 4 && i0 + j < n_red; ++j) {    // ragged end of the vector, or a group straddling W_0's edge
+      const int i = i0 + j;
+      d.P[i] = pp[j]; d.s0[i] = mm[j]; d.s1[i] = vv[j];
+      if (i < d.wb_skip_lo || i >= d.wb_skip_hi) d.Wb[i] = __float2bfloat16(pp[j]);
+    }
+  };
+  auto load_group = [&](int gq, float4& p4, float4& m4, float4& v4) {
+    const int i0 = 4 * gq;
+    if (i0 + 4 <= d.n) {                               // (n_red = n - 1: the vectors hold one more element)
+      p4 = *reinterpret_cast<const float4*>(d.P + i0);
+      m4 = *reinterpret_cast<const float4*>(d.s0 + i0);
+      v4 = *reinterpret_cast<const float4*>(d.s1 + i0);
+    } else {
+      float* pp = &p4.x; float* mm = &m4.x; float* vv = &v4.x;
+      for (int j = 0; j < 4; ++j) {
+        const bool in = i0 + j < d.n;
+        pp[j] = in ? d.P[i0 + j] : 0.f; mm[j] = in ? d.s0[i0 + j] : 0.f; vv[j] = in ? d.s1[i0 + j] : 0.f;
+      }
+    }
+  };
   for (int q = 0; q < N; ++q) {
     const int lo = q * c4 + cta * per2, hi = min(min(lo + per2, (q + 1) * c4), n4);
-    for (int gq = lo + threadIdx.x; gq < hi; gq += blockDim.x) {
-      const float4 sum = ld_volatile_f4(my_dP + 4 * size_t(gq));
-      const float gr[4] = {sum.x * inv_n, sum.y * inv_n, sum.z * inv_n, sum.w * inv_n};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int i = 4 * gq + j;
-        if (i >= n_red) break;
-        float p = d.P[i], m = d.s0[i], v = d.s1[i];
-        opt_apply(c, gr[j], p, m, v);
-        d.P[i] = p; d.s0[i] = m; d.s1[i] = v;
-        if (i < d.wb_skip_lo || i >= d.wb_skip_hi) d.Wb[i] = __float2bfloat16(p);
-        if (i == d.n - 2) {                            // fm_bias shares b_out's gradient
-          float p2 = d.P[d.n - 1], m2 = d.s0[d.n - 1], v2 = d.s1[d.n - 1];
-          opt_apply(c, gr[j], p2, m2, v2);
-          d.P[d.n - 1] = p2; d.s0[d.n - 1] = m2; d.s1[d.n - 1] = v2;
-        }
-      }
+    for (int gq = lo + threadIdx.x; gq < hi; gq += 2 * blockDim.x) {
+      const int g1 = gq + blockDim.x;
+      const bool two = g1 < hi;
+      float4 sa = ld_volatile_f4(my_dP + 4 * size_t(gq)), sb = make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 pa4, ma4, va4, pb4, mb4, vb4;
+      load_group(gq, pa4, ma4, va4);
+      if (two) { sb = ld_volatile_f4(my_dP + 4 * size_t(g1)); load_group(g1, pb4, mb4, vb4); }
+      apply_group(gq, sa, pa4, ma4, va4);
+      store_group(gq, pa4, ma4, va4);
+      if (two) { apply_group(g1, sb, pb4, mb4, vb4); store_group(g1, pb4, mb4, vb4); }
     }
   }
   stamp(cv, cta, 11);
