@@ -553,7 +553,9 @@ extern "C" int dfm_engine_comm_attach(void* h, int world, int rank, void* const*
                                       void* const* grad_ptrs, void* grad_mc) {
   Engine* E = static_cast<Engine*>(h);
   DFM_REQUIRE(block_ptrs && fm_v_ptrs && fm_w_ptrs, "dfm_engine_comm_attach: null pointer table");
-  int dense_ctas = 32;
+  // the dense kernel shares the GPU with the sparse exchange (one 1024-thread CTA per SM each): enough CTAs that its
+  // optimizer pass (26 bytes per parameter) ends before the exchange does, no more
+  int dense_ctas = std::min(48, std::max(24, E->n_dense / 11000));
   if (const char* v = getenv("DFM_DENSE_CTAS")) dense_ctas = atoi(v);
   // one 1024-thread CTA per SM, all resident at once, beside the dense kernel's CTAs
   int rc = comm_prepare(*E, world, rank, 148 - dense_ctas, dense_ctas);
