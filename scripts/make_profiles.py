@@ -16,7 +16,8 @@ LIB = os.path.join(ROOT, "deepfm-tensorflow-distributed-training-on-amazon-sagem
 OUT = os.path.join(ROOT, "profiles")
 os.makedirs(OUT, exist_ok=True)
 
-MNEMONICS = ["UTCHMMA", "UTCBAR", "UTMALDG", "UTMAPF", "LDTM", "UTCATOMSWS", "SYNCS", "STG.E.ENL2.256", "REDG", "RED.E",
+MNEMONICS = ["UTCHMMA", "UTCBAR", "UTMALDG", "UTMAPF", "LDTM", "UTCATOMSWS", "SYNCS", "LDGMC", "STG.E.128.STRONG.SYS",
+             "STG.E.STRONG.SYS", "STG.E.ENL2.256", "REDG", "RED.E",
              "ATOMG", "LDG", "STG", "MEMBAR.SC.SYS", "MEMBAR.ALL.SYS", "HMMA", "FFMA"]
 
 
@@ -42,8 +43,9 @@ def sass_summary():
         f.write("SASS mnemonic counts per kernel of libdfm_cuda.so (cuobjdump -sass, sm_100a).\n"
                 "UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG = TMA tensor load, UTCBAR = tcgen05.commit,\n"
                 "UTCATOMSWS = TMEM alloc, SYNCS = mbarrier ops, STG.E.ENL2.256 = 256-bit store, REDG = red.global.\n"
-                "comm.cu kernels use plain LDG/STG on IPC-mapped peer pointers plus ld.acquire/st.release .sys\n"
-                "(MEMBAR.*.SYS) -- NVLink traffic is ordinary loads/stores in SASS.\n\n")
+                "comm.cu: LDGMC.E.ADD.F32x4 = multimem.ld_reduce (the sum is formed inside the NVSwitch), multimem.st is a\n"
+                "STG.E.128.STRONG.SYS on the multicast address; peer loads / stores and the flag protocol are ordinary\n"
+                "LDG / STG plus ld.acquire / st.release at system scope (MEMBAR.*.SYS).\n\n")
         for k, c in per.items():
             if c["_total"] < 8:
                 continue
@@ -99,7 +101,9 @@ def sass_listings():
     """Full SASS of the kernels BASELINE.json asks to see: the fused collective kernel and one tcgen05 GEMM."""
     txt = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
     blocks = re.split(r"(?=\t\tFunction : )", txt)
-    for key, fname in (("exchange_apply_kernel", "sass_exchange_apply_kernel.txt"),
+    for key, fname in (("exchange_apply_kernelILb0", "sass_exchange_apply_kernel.txt"),
+                       ("dense_sync_kernelILb0", "sass_dense_sync_kernel.txt"),
+                       ("allreduce_kernel", "sass_allreduce_kernel.txt"),
                        ("mlp_layer_kernelILb0", "sass_mlp_layer_fwd_kernel.txt"),
                        ("embed_bwd_kernel", "sass_embed_bwd_kernel.txt")):
         for b in blocks:
