@@ -54,6 +54,8 @@ struct BatchWork {
 
 // A byte range of a mapped file whose framing one worker walks.
 struct Chunk {
+  std::shared_ptr<RecordSource> src;        // keeps the mapping alive: on stop / failure the batcher abandons ranges that
+                                            // a worker may still be walking
   const uint8_t* base = nullptr;
   size_t size = 0, begin = 0, end = 0;
   bool verify = false;
@@ -239,7 +241,7 @@ class Loader {
     for (size_t ci = 0; ci < n_chunks; ++ci) {
       while (next_chunk < n_chunks && inflight.size() < window) {
         auto c = std::make_shared<Chunk>();
-        c->base = base; c->size = size; c->verify = cfg_.verify_crc != 0; c->path = path.c_str();
+        c->src = src; c->base = base; c->size = size; c->verify = cfg_.verify_crc != 0; c->path = path.c_str();
         c->begin = next_chunk * kIndexChunk;
         c->end = std::min(size, c->begin + kIndexChunk);
         {

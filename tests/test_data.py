@@ -276,3 +276,19 @@ def test_parallel_framing_index_matches_sequential_read(tmp_path):
         want = ref_ids[shard[1]::shard[0]]
         assert got.shape[0] == 2 * want.shape[0]
         assert np.array_equal(got[:want.shape[0]], want) and np.array_equal(got[want.shape[0]:], want)
+
+
+def test_loader_can_be_closed_mid_stream(tmp_path):
+    """Closing a loader that still has framing-index ranges in flight must not touch an unmapped file (regression:
+    the batcher dropped the mapping while a worker was still walking it)."""
+    import torch
+    from deepfm_b200.data.loader import BatchLoader
+    from deepfm_b200.data.tfrecord import generate_synthetic
+    path = str(tmp_path / "big.tfrecords")
+    generate_synthetic(path, 40000, 39, 117581, n_dense=13, seed=5)      # ~12 MB: a dozen index ranges
+    for it in range(40):
+        ld = BatchLoader([path], 39, 512, num_epochs=1000, num_workers=6, num_slots=4, ids_dtype=torch.int32)
+        for i, _ in enumerate(ld):
+            if i == it % 5:
+                break
+        ld.close()
