@@ -59,8 +59,7 @@ struct Engine {
   cudaGraphExec_t graph[kPipe] = {nullptr, nullptr};
   uint8_t* in_slab[kPipe] = {nullptr, nullptr};     // [ids | vals | labels] for batch_max rows
   size_t slab_bytes = 0, off_vals = 0, off_labels = 0;
-  cudaStream_t copy_stream = nullptr;
-  cudaEvent_t ev_h2d[kPipe] = {nullptr, nullptr}, ev_done[kPipe] = {nullptr, nullptr};
+  cudaEvent_t ev_done[kPipe] = {nullptr, nullptr};
   long long pipe_step = 0;
   // pipelined flavours of the step graph: beside the kernels that train on slab w, a memcpy node prefetches the
   // NEXT batch into slab 1-w, and another copies the loss sum into a pinned ring -- no cross-stream events and no
@@ -398,14 +397,12 @@ extern "C" int dfm_engine_destroy(void* h) {
   if (E->ev_dedupe) cudaEventDestroy(E->ev_dedupe);
   for (int i = 0; i < Engine::kPipe; ++i) {
     if (E->graph[i]) cudaGraphExecDestroy(E->graph[i]);
-    if (E->ev_h2d[i]) cudaEventDestroy(E->ev_h2d[i]);
     if (E->ev_done[i]) cudaEventDestroy(E->ev_done[i]);
     for (int k = 0; k < 2; ++k) {
       if (E->pf_exec[i][k]) cudaGraphExecDestroy(E->pf_exec[i][k]);
       if (E->pf_graph[i][k]) cudaGraphDestroy(E->pf_graph[i][k]);
     }
   }
-  if (E->copy_stream) cudaStreamDestroy(E->copy_stream);
   if (E->pf_stream) cudaStreamDestroy(E->pf_stream);
   if (E->ev_pf_fork) cudaEventDestroy(E->ev_pf_fork);
   if (E->ev_pf_join) cudaEventDestroy(E->ev_pf_join);
@@ -673,12 +670,8 @@ extern "C" int dfm_engine_capture(void* h, dfm_stream_t s_) {
       int rc = E->alloc(&E->in_slab[i], E->slab_bytes);
       if (rc) return rc;
     }
-    if (!E->ev_h2d[i]) {
-      DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_h2d[i], cudaEventDisableTiming));
-      DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_done[i], cudaEventDisableTiming));
-    }
+    if (!E->ev_done[i]) DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_done[i], cudaEventDisableTiming));
   }
-  if (!E->copy_stream) DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&E->copy_stream, cudaStreamNonBlocking));
   if (!E->pf_stream) {
     DFM_CUDA_CHECK(cudaStreamCreateWithFlags(&E->pf_stream, cudaStreamNonBlocking));
     DFM_CUDA_CHECK(cudaEventCreateWithFlags(&E->ev_pf_fork, cudaEventDisableTiming));
@@ -823,27 +816,6 @@ extern "C" int dfm_engine_slab_ptr(void* h, int which, void** ptr) {
   Engine* E = static_cast<Engine*>(h);
   DFM_REQUIRE(which >= 0 && which < Engine::kPipe && E->in_slab[which], "dfm_engine_slab_ptr: capture first");
   *ptr = E->in_slab[which];
-  return DFM_OK;
-}
-
-// One end-to-end step from pinned host memory (or from another device buffer: the copy kind is inferred
-// from the pointer): the batch is copied on the copy stream (overlapping the previous step's kernels), graph replay on `stream`, D2H of the loss sum into `loss_host` (pinned).
-extern "C" int dfm_engine_step_from_host(void* h, const void* host_slab, float* loss_host, dfm_stream_t s_) {
-  Engine* E = static_cast<Engine*>(h);
-  cudaStream_t s = static_cast<cudaStream_t>(s_);
-  const int w = int(E->pipe_step % Engine::kPipe);
-  DFM_REQUIRE(E->graph[w] != nullptr, "dfm_engine_step_from_host: capture first");
-  E->staged_src[0] = E->staged_src[1] = nullptr;
-  // slab w was last read by step (pipe_step - kPipe)
-  if (E->pipe_step >= Engine::kPipe) DFM_CUDA_CHECK(cudaStreamWaitEvent(E->copy_stream, E->ev_done[w], 0));
-  DFM_CUDA_CHECK(cudaMemcpyAsync(E->in_slab[w], host_slab, E->slab_bytes, cudaMemcpyDefault, E->copy_stream));
-  DFM_CUDA_CHECK(cudaEventRecord(E->ev_h2d[w], E->copy_stream));
-  DFM_CUDA_CHECK(cudaStreamWaitEvent(s, E->ev_h2d[w], 0));
-  DFM_CUDA_CHECK(cudaGraphLaunch(E->graph[w], s));
-  DFM_CUDA_CHECK(cudaEventRecord(E->ev_done[w], s));
-  if (loss_host)
-    DFM_CUDA_CHECK(cudaMemcpyAsync(loss_host, &E->st->loss_sum, sizeof(float), cudaMemcpyDeviceToHost, s));
-  E->pipe_step++;
   return DFM_OK;
 }
 

@@ -177,7 +177,6 @@ class FusedEngine:
         lib.dfm_engine_capture.argtypes = [C.c_void_p, C.c_void_p]
         lib.dfm_engine_slab_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
         lib.dfm_engine_replay.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
-        lib.dfm_engine_step_from_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.dfm_engine_step_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_void_p]
         lib.dfm_engine_reset_pipeline.argtypes = [C.c_void_p]
         lib.dfm_engine_loss_ring.argtypes = [C.c_void_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int)]
@@ -369,12 +368,6 @@ class FusedEngine:
 
     def replay(self, which: int = 0) -> None:
         _native.check(self._lib.dfm_engine_replay(self._h, which, self._stream()), "dfm_engine_replay")
-
-    def step_from_host(self, host_slab: torch.Tensor, loss_host: Optional[torch.Tensor] = None) -> None:
-        """End-to-end step: pinned host slab -> device (copy stream) -> graph replay -> loss to pinned host."""
-        _native.check(self._lib.dfm_engine_step_from_host(
-            self._h, host_slab.data_ptr(), loss_host.data_ptr() if loss_host is not None else None,
-            self._stream()), "dfm_engine_step_from_host")
 
     def step_pipelined(self, cur: torch.Tensor, nxt: Optional[torch.Tensor] = None) -> int:
         """Trains on slab ``cur`` while the graph's prefetch node copies ``nxt`` (pinned host or device slab)

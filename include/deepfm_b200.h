@@ -109,9 +109,6 @@ int dfm_engine_slab_layout(void* engine, long long* bytes, long long* off_vals, 
 int dfm_engine_capture(void* engine, dfm_stream_t stream);
 int dfm_engine_slab_ptr(void* engine, int which, void** ptr);
 int dfm_engine_replay(void* engine, int which, dfm_stream_t stream);
-/* One end-to-end step: async H2D of `host_slab` (pinned) on an internal copy stream, graph replay on
- * `stream`, async D2H of the batch loss sum into `loss_host` (pinned, may be NULL). */
-int dfm_engine_step_from_host(void* engine, const void* host_slab, float* loss_host, dfm_stream_t stream);
 /* Pipelined step: trains on `cur` (a full batch slab, pinned host or device memory) and copies `next` (same
  * kinds, or NULL) into the other input slab beside the kernels, as a node of the same graph; the next call
  * should then pass that pointer as `cur`.  A `cur` that was not prefetched is copied in stream order first.
