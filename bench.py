@@ -404,6 +404,8 @@ def main():
     sampler = ClockSampler(local_rank)
     sampler.start()
     nv0 = nvlink_kib(local_rank) if world > 1 else None
+    cnt0 = (trainer.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)[20:23].tolist()
+            if world > 1 and trainer.backend == "fused" else None)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -413,6 +415,8 @@ def main():
     barrier()
     clocks = sampler.stop()
     nv1 = nvlink_kib(local_rank) if nv0 else None
+    cnt1 = (trainer.engine.buffer("comm_dbg", dtype="i4").clone().cpu().view(torch.int64)[20:23].tolist()
+            if cnt0 is not None else None)
     ms_dev = e0.elapsed_time(e1)
     del dev_pool
     if os.environ.get("DFM_BENCH_TIMELINE") and trainer.backend == "fused" and rank == 0:
@@ -502,6 +506,22 @@ def main():
         out["worst_rel_update_err_vs_nccl"] = check["worst_rel_update_err_vs_nccl"]
         out["comm"] = {"provider": check["provider"], "nvls_dense": bool(check["multicast"] & 1),
                        "nvls_rows": bool(check["multicast"] & 2)}
+    if cnt0 is not None:
+        # NVLink bytes per step of this rank, from what its kernels COUNTED (records pushed to peers, rows published) --
+        # `nvidia-smi nvlink -gt d` reads N/A in this pool's containers, so the link counters cannot be sampled
+        steps = max(cnt1[2] - cnt0[2], 1)
+        rows, recs = (cnt1[0] - cnt0[0]) / steps, (cnt1[1] - cnt0[1]) / steps
+        mc = bool(check and check["multicast"] & 2)
+        rec_b, row_b = 4 * EMB + 8, 4 * EMB + 4
+        t2 = torch.tensor([rows, recs], device=dev, dtype=torch.float64)
+        dist.all_reduce(t2)
+        dense_b = 4 * trainer.engine.n_dense * 2.0 * (world - 1) / world       # reduce-scatter + all-gather, each way
+        out["nvlink_bytes_per_step"] = {
+            "sparse_tx": recs * rec_b + rows * row_b * (1 if mc else world - 1),
+            "sparse_rx": (float(t2[1]) / world) * rec_b + (float(t2[0]) - rows) * row_b,
+            "dense_each_way": dense_b, "rank": rank, "records_pushed_to_peers": recs, "rows_published": rows,
+            "how": "sparse: counted by the exchange kernel (records pushed, rows published; rx from the other ranks' counts); "
+                   "dense: size of the vector; the GPUs' link counters read N/A in this pool's containers"}
     if nv0 and nv1:
         # measured by the NVLink counters of this rank's GPU around the device-timed region (KiB granularity)
         out["nvlink_bytes_per_step"] = {"tx": (nv1[0] - nv0[0]) * 1024 / K, "rx": (nv1[1] - nv0[1]) * 1024 / K,

@@ -432,6 +432,7 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
   // Each record is a chain: id -> entries of all senders -> {senders' rows, my table row + slots} -> update ->
   // stores.  The lowest-ranked sender's record carries the row; the other records of the id do nothing.
   const unsigned grp_mask = LPR >= 32 ? 0xffffffffu : ((1u << LPR) - 1u);
+  unsigned int n_own = 0;                              // rows this warp published (counted by lane 0)
   for (int it0 = 0; it0 < n_items; it0 += kRows) {
     int id[kRows], rr[kRows], ent[kRows];
     bool any = false;
@@ -481,6 +482,7 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
     }
 #pragma unroll
     for (int j = 0; j < kRows; ++j) {
+      n_own += __popc(__ballot_sync(0xffffffffu, own[j] && sub == 0));
       if (!own[j]) continue;
       if (cv.exact) {
         // dense_exact: publish the summed gradient row; every replica sweeps its whole table afterwards
@@ -516,6 +518,23 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
           *reinterpret_cast<float4*>(cv.tab_v[r] + pi) = p[j];
           if (sub == 0) cv.tab_w[r][id[j]] = pw[j];
         }
+      }
+    }
+  }
+  // traffic counters (cumulative since attach; read by bench.py around its timed region): one atomic per CTA
+  {
+    __shared__ unsigned int rows_cta;
+    if (threadIdx.x == 0) rows_cta = 0;
+    __syncthreads();
+    if (lane == 0 && n_own) atomicAdd(&rows_cta, n_own);
+    __syncthreads();
+    if (threadIdx.x == 0 && cv.dbg) {
+      if (rows_cta) atomicAdd(cv.dbg + 20, static_cast<unsigned long long>(rows_cta));       // rows I published
+      if (cta == 0) {
+        unsigned long long sent = 0;
+        for (int o = 0; o < N; ++o) if (o != me) sent += unsigned(a.st->n_seg[o]);
+        cv.dbg[21] += sent;                                                                // records I pushed to peers
+        cv.dbg[22] += 1;                                                                   // steps
       }
     }
   }
