@@ -34,6 +34,7 @@ def test_fused_collectives_two_ranks(opt, env):
     assert len(results) == 2 and all(r["ok"] for r in results)
     for r in results:
         assert all(v for k, v in r.items() if k.startswith("identical:"))
+        assert r.get("stress_2000_steps_identical", True)      # delayed-rank stress of the flag protocol
         if opt == "GD":
             assert r["worst_rel_update_err"] < 0.05
 
