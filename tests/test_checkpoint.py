@@ -93,3 +93,114 @@ def test_bundle_roundtrip_property(tmp_path_factory, seed, n_vars):
     assert set(r) == set(t)
     for k in t:
         assert r[k].dtype == t[k].dtype and r[k].shape == t[k].shape and np.array_equal(r[k], t[k]), k
+
+
+# ---------------------------------------------------------------------------------------------------
+# An index file assembled BY HAND from the published formats (LevelDB table_format.md; tensor_bundle.proto), with
+# none of the module's own encoding helpers: if the module reads it, and this file's own little parser reads what the
+# module writes, reader and writer agree with the spec and not merely with each other.  (No TensorFlow exists for this
+# Python, so a TF-written golden file cannot be produced here: DESIGN.md section 6 says "unverified against TF".)
+# ---------------------------------------------------------------------------------------------------
+def _crc32c(data: bytes) -> int:
+    crc = 0xFFFFFFFF
+    for b in data:
+        crc ^= b
+        for _ in range(8):
+            crc = (crc >> 1) ^ (0x82F63B78 & -(crc & 1))
+    return crc ^ 0xFFFFFFFF
+
+
+def _masked(data: bytes) -> int:
+    c = _crc32c(data)
+    return (((c >> 15) | (c << 17)) + 0xA282EAD8) & 0xFFFFFFFF
+
+
+def _vi(v: int) -> bytes:
+    out = b""
+    while v >= 0x80:
+        out += bytes([(v & 0x7F) | 0x80])
+        v >>= 7
+    return out + bytes([v])
+
+
+def _block(entries) -> bytes:
+    """One LevelDB block with a restart point at every entry (shared = 0), then the restart array and its length."""
+    body, restarts = b"", []
+    for k, v in entries:
+        restarts.append(len(body))
+        body += _vi(0) + _vi(len(k)) + _vi(len(v)) + k + v
+    return body + b"".join(struct.pack("<I", r) for r in restarts) + struct.pack("<I", len(restarts))
+
+
+def _with_trailer(block: bytes) -> bytes:
+    return block + b"\x00" + struct.pack("<I", _masked(block + b"\x00"))      # type 0 = uncompressed, masked CRC32C
+
+
+def _hand_made_index(value_bytes: bytes) -> bytes:
+    header = bytes([0x08, 0x01, 0x1A, 0x02, 0x08, 0x01])          # BundleHeaderProto{num_shards: 1, version{producer: 1}}
+    shape = bytes([0x12, 0x02, 0x08, 0x03])                        # TensorShapeProto{dim{size: 3}}
+    entry = bytes([0x08, 0x01]) + bytes([0x12, len(shape)]) + shape + bytes([0x28, len(value_bytes)]) + \
+        bytes([0x35]) + struct.pack("<I", _masked(value_bytes))    # dtype DT_FLOAT, shape, size, crc32c (fixed32)
+    data = _with_trailer(_block([(b"", header), (b"fm_w", entry)]))
+    meta_off = len(data)
+    meta = _with_trailer(_block([]) if False else struct.pack("<II", 0, 1))   # empty block: restarts [0], count 1
+    index_off = meta_off + len(meta)
+    index = _with_trailer(_block([(b"fm_x", _vi(0) + _vi(len(data) - 5))]))    # separator >= last key -> handle of block 0
+    footer = _vi(meta_off) + _vi(len(meta) - 5) + _vi(index_off) + _vi(len(index) - 5)
+    footer += b"\x00" * (40 - len(footer)) + struct.pack("<Q", 0xDB4775248B80FB57)
+    return data + meta + index + footer
+
+
+def _spec_parse_index(raw: bytes):
+    """Minimal reader straight from table_format.md: footer -> index block -> data blocks -> (key, value) pairs."""
+    def vi(buf, pos):
+        v = shift = 0
+        while True:
+            b = buf[pos]; pos += 1
+            v |= (b & 0x7F) << shift
+            if b < 0x80:
+                return v, pos
+            shift += 7
+
+    def block(off, size):
+        blk = raw[off:off + size]
+        assert struct.unpack("<I", raw[off + size + 1:off + size + 5])[0] == _masked(raw[off:off + size + 1])
+        n_restarts = struct.unpack("<I", blk[-4:])[0]
+        end = len(blk) - 4 - 4 * n_restarts
+        pos, key, out = 0, b"", []
+        while pos < end:
+            shared, pos = vi(blk, pos); non_shared, pos = vi(blk, pos); vlen, pos = vi(blk, pos)
+            key = key[:shared] + blk[pos:pos + non_shared]; pos += non_shared
+            out.append((key, blk[pos:pos + vlen])); pos += vlen
+        return out
+
+    assert struct.unpack("<Q", raw[-8:])[0] == 0xDB4775248B80FB57
+    f = raw[-48:-8]
+    _, p = vi(f, 0); _, p = vi(f, p)
+    ioff, p = vi(f, p); isz, p = vi(f, p)
+    items = []
+    for _, handle in block(ioff, isz):
+        o, q = vi(handle, 0); s, _ = vi(handle, q)
+        items += block(o, s)
+    return items
+
+
+def test_reader_accepts_an_index_assembled_from_the_format_spec(tmp_path):
+    vals = np.asarray([1.5, -2.0, 3.25], np.float32)
+    prefix = str(tmp_path / "model.ckpt-1")
+    open(prefix + ".index", "wb").write(_hand_made_index(vals.tobytes()))
+    open(prefix + ".data-00000-of-00001", "wb").write(vals.tobytes())
+    r = ck.read_bundle(prefix)
+    assert list(r) == ["fm_w"] and r["fm_w"].dtype == np.float32 and np.array_equal(r["fm_w"], vals)
+
+
+def test_writer_output_parses_with_a_reader_built_from_the_format_spec(tmp_path):
+    prefix = str(tmp_path / "m")
+    t = _tensors()
+    ck.write_bundle(prefix, t)
+    items = _spec_parse_index(open(prefix + ".index", "rb").read())
+    keys = [k for k, _ in items]
+    assert keys[0] == b"" and keys[1:] == sorted(k.encode() for k in t)          # header entry first, then sorted names
+    assert items[0][1][:2] == bytes([0x08, 0x01])                                # BundleHeaderProto.num_shards = 1
+    entry = dict(items)[b"fm_v"]
+    assert entry[:2] == bytes([0x08, 0x01]) and bytes([0x12]) in entry           # DT_FLOAT, then the shape message
