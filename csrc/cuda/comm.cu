@@ -65,6 +65,19 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
 __device__ __forceinline__ void red_release_gpu_add(unsigned int* p, unsigned int v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void red_release_sys_add_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
   float4 v;
   asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
@@ -130,6 +143,46 @@ __device__ __forceinline__ void cta_wait_all_ranks(const CommView& cv, int cta, 
     while (ld_relaxed_sys(mine) < epoch)
       if (clock64() - t0 > cv.watchdog) comm_watchdog_trip(cv.rank, cta, which < 2 ? 2 : 0, t, epoch);
     (void)ld_acquire_sys(mine);        // one acquire once the flag is up: peers' writes are visible from here
+  }
+  __syncthreads();
+}
+
+// Barrier among ALL CTAs of ALL ranks, hierarchical: the CTAs of a rank meet at a local counter (gpu scope, a
+// non-returning reduction each), CTA 0 alone talks to the other GPUs -- one system-scope release per peer, whose fence
+// is cumulative over everything the local CTAs wrote before they arrived -- and then opens a local gate.  Measured
+// here: a system-scope release from every one of 116 CTAs costs 10-12 us per barrier, from 32 CTAs 5-8 us; the fence is
+// the expensive part, so only one CTA pays it.  `local` = {arrival counter, gate} of this barrier in local memory.
+__device__ __forceinline__ void hier_barrier_all(const CommView& cv, int cta, int which, unsigned int epoch,
+                                                 unsigned int* local) {
+  __syncthreads();
+  const unsigned int gen = epoch - cv.epoch_base;                 // barriers passed so far, this one included
+  if (cta != 0) {
+    if (threadIdx.x == 0) {
+      red_release_gpu_add(local, 1u);
+      const long long t0 = clock64();
+      while (ld_acquire_gpu(local + 1) < gen)
+        if (clock64() - t0 > cv.watchdog) comm_watchdog_trip(cv.rank, cta, 1, -1, epoch);
+    }
+  } else {
+    if (threadIdx.x == 0) {
+      const unsigned int target = gen * unsigned(cv.ctas - 1);
+      const long long t0 = clock64();
+      while (ld_acquire_gpu(local) < target)
+        if (clock64() - t0 > cv.watchdog) comm_watchdog_trip(cv.rank, cta, 1, -1, epoch);
+    }
+    __syncthreads();
+    if (threadIdx.x < cv.world) {
+      unsigned int* peer_flags = reinterpret_cast<unsigned int*>(cv.base[threadIdx.x] + cv.off_flags + which * cv.flags_bytes);
+      st_release_sys(peer_flags + size_t(cv.rank) * kCommMaxCtas, epoch);
+      const unsigned int* mine = reinterpret_cast<const unsigned int*>(cv.base[cv.rank] + cv.off_flags + which * cv.flags_bytes) +
+                                 size_t(threadIdx.x) * kCommMaxCtas;
+      const long long t0 = clock64();
+      while (ld_relaxed_sys(mine) < epoch)
+        if (clock64() - t0 > cv.watchdog) comm_watchdog_trip(cv.rank, cta, 0, threadIdx.x, epoch);
+      (void)ld_acquire_sys(mine);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(local + 1), "r"(gen) : "memory");
   }
   __syncthreads();
 }
@@ -371,6 +424,9 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
         if (sub == 0) {
           reinterpret_cast<uint2*>(cv.base[o] + cv.off_in_tails)[size_t(me) * cap + sidx[j]] =
               make_uint2(__float_as_uint(gw[j]), uint32_t(id[j]));
+          // the owner's (id, sender) index entry, written from here: the owner needs no index pass of its own
+          reinterpret_cast<unsigned long long*>(cv.base[o] + cv.off_entries)[size_t(id[j]) - o + me] =
+              (static_cast<unsigned long long>(epoch) << 32) | unsigned(sidx[j] + 1);
           grow[Ke] = 0.f;
           a.slot_of[id[j]] = -1;
         }
@@ -380,14 +436,17 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
   if (threadIdx.x < N)
     reinterpret_cast<int*>(cv.base[threadIdx.x] + cv.off_in_count)[me * kCommMaxCtas + cta] = a.st->n_seg[threadIdx.x];
   stamp(cv, cta, 1);
-  cta_signal_all_ranks(cv, cta, 2, epoch);
-  cta_wait_all_ranks(cv, cta, 2, epoch);
+  // ---------------- barrier: ALL CTAs of ALL ranks have pushed ----------------
+  // a cross-GPU barrier and a grid barrier in one, so the merge below may read any record and any index entry
+  hier_barrier_all(cv, cta, 2, epoch, x.bar_local);
   stamp(cv, cta, 2);
+  stamp(cv, cta, 3);
+  stamp(cv, cta, 4);
 
-  // ---------------- phase 1: index the records I received by (id, sender) ----------------
   const int* in_count = reinterpret_cast<const int*>(cv.base[me] + cv.off_in_count);
   const float* in_grads = reinterpret_cast<const float*>(cv.base[me] + cv.off_in_grads);
   const uint2* in_tails = reinterpret_cast<const uint2*>(cv.base[me] + cv.off_in_tails);
+  const unsigned long long* entry_of = reinterpret_cast<const unsigned long long*>(cv.base[me] + cv.off_entries);
   int nr_l = lane < N ? ld_volatile_i(in_count + lane * kCommMaxCtas + cta) : 0;   // records sender `lane` pushed
   int ng_max = (nr_l + G - 1) / G;
 #pragma unroll
@@ -401,32 +460,6 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
     const int first = (warp_g - ((r + me) % N) * stripe + warps) % warps;
     return (k * warps + first) * G + g;
   };
-  for (int it0 = 0; it0 < n_items; it0 += kPush) {     // all ids first, then all entries
-    int id[kPush], rs[kPush], ss[kPush];
-#pragma unroll
-    for (int j = 0; j < kPush; ++j) {
-      int nr;
-      ss[j] = item_record(min(it0 + j, n_items - 1), rs[j], nr);
-      const bool on = lane_on && sub == 0 && it0 + j < n_items && ss[j] < nr;
-      id[j] = on ? int(__ldcg(reinterpret_cast<const unsigned int*>(in_tails + size_t(rs[j]) * cap + ss[j]) + 1)) : -1;
-    }
-#pragma unroll
-    for (int j = 0; j < kPush; ++j)
-      if (id[j] >= 0)
-        x.entry_of[size_t(id[j]) - me + rs[j]] = (static_cast<unsigned long long>(epoch) << 32) | unsigned(ss[j] + 1);
-  }
-  stamp(cv, cta, 3);
-  // grid barrier among this rank's CTAs (co-resident)
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    red_release_gpu_add(x.grid_bar, 1u);
-    const unsigned int target = epoch * unsigned(cv.ctas);
-    const long long t0 = clock64();
-    while (ld_acquire_gpu(x.grid_bar) < target)
-      if (clock64() - t0 > cv.watchdog) comm_watchdog_trip(me, cta, 1, -1, epoch);
-  }
-  __syncthreads();
-  stamp(cv, cta, 4);
 
   // ---------------- phase 2: owners merge, apply, publish ----------------
   // Each record is a chain: id -> entries of all senders -> {senders' rows, my table row + slots} -> update ->
@@ -449,7 +482,7 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
     for (int j = 0; j < kRows; ++j) {
       ent[j] = 0;
       if (id[j] >= 0 && sub < N) {                     // lane sub reads the entry of sender sub
-        const unsigned long long e = __ldcg(x.entry_of + size_t(id[j]) - me + sub);
+        const unsigned long long e = __ldcg(entry_of + size_t(id[j]) - me + sub);
         if (unsigned(e >> 32) == epoch) ent[j] = int(unsigned(e));
       }
     }
@@ -540,8 +573,7 @@ exchange_apply_kernel(const __grid_constant__ XchgArgs pa, const XchgArgs* __res
   }
   stamp(cv, cta, 5);
   // every replica must hold every row before the next step gathers from the tables
-  cta_signal_all_ranks(cv, cta, 3, epoch);
-  cta_wait_all_ranks(cv, cta, 3, epoch);
+  hier_barrier_all(cv, cta, 3, epoch, x.bar_local + 2);
   stamp(cv, cta, 6);
   if (threadIdx.x == 0) kstamp_any(a.st, kStampSparseEnd);
 }

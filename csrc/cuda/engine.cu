@@ -496,6 +496,8 @@ static size_t comm_layout(const Engine& E, int world, CommView* cv) {
   v.off_in_count = o;  o = align256(o + size_t(world) * kCommMaxCtas * 4);
   v.off_in_tails = o;  o = align256(o + size_t(world) * cap * 8);
   v.off_in_grads = o;  o = align256(o + size_t(world) * cap * E.cfg.embedding_size * 4);
+  v.off_entries = o;   o = align256(o + (size_t(E.cfg.feature_size) + world) * 8);
+  v.off_counter = o;   o += 256;
   return o;
 }
 
@@ -522,15 +524,20 @@ static int comm_prepare(Engine& E, int world, int rank, int ctas, int dense_ctas
   if ((rc = E.alloc(&E.uniq_ids, size_t(world) * cap))) return rc;
   XchgArgs& x = E.xa;
   x = XchgArgs{};
-  if ((rc = E.alloc(&x.entry_of, size_t(E.cfg.feature_size) + world))) return rc;
-  if ((rc = E.alloc(&x.grid_bar, 64))) return rc;
   if ((rc = E.alloc(&E.comm_dbg, 32))) return rc;
+  if ((rc = E.alloc(&x.bar_local, 64))) return rc;
   CommView& cv = x.cv;
   comm_layout(E, world, &cv);
   cv.world = world; cv.rank = rank; cv.cap = int(cap);
   cv.ctas = ctas; cv.dense_ctas = dense_ctas;
   cv.dbg = E.comm_dbg;
   cv.exact = E.cfg.table_update_mode == DFM_TABLE_DENSE_EXACT;
+  {
+    StepState now{};
+    DFM_CUDA_CHECK(cudaDeviceSynchronize());
+    DFM_CUDA_CHECK(cudaMemcpy(&now, E.st, sizeof(now), cudaMemcpyDeviceToHost));
+    cv.epoch_base = unsigned(now.comm_epoch);
+  }
   double secs = 120.0;     // a rank may legitimately stall this long on the host (checkpoint, input) while its peers wait
   if (const char* v = getenv("DFM_COMM_TIMEOUT_S")) secs = atof(v);
   cv.watchdog = (long long)(std::max(secs, 0.001) * 1.9e9);
@@ -555,7 +562,9 @@ extern "C" int dfm_engine_comm_attach(void* h, int world, int rank, void* const*
   int dense_ctas = std::min(48, std::max(24, E->n_dense / 11000));
   if (const char* v = getenv("DFM_DENSE_CTAS")) dense_ctas = atoi(v);
   // one 1024-thread CTA per SM, all resident at once, beside the dense kernel's CTAs
-  int rc = comm_prepare(*E, world, rank, 148 - dense_ctas, dense_ctas);
+  int xchg_ctas = 148 - dense_ctas;
+  if (const char* v = getenv("DFM_XCHG_CTAS")) xchg_ctas = std::max(world, std::min(atoi(v), 148 - dense_ctas));
+  int rc = comm_prepare(*E, world, rank, xchg_ctas, dense_ctas);
   if (rc) return rc;
   CommView& cv = E->xa.cv;
   DFM_REQUIRE(fm_v_ptrs[rank] == E->t.fm_v && fm_w_ptrs[rank] == E->t.fm_w,

@@ -288,9 +288,14 @@ struct CommView {
   int cap;            // inbox rows per sender and slots per owner segment (= batch_max * field_size)
   int ctas;           // CTAs per rank of the sparse exchange kernel (all co-resident)
   int dense_ctas;     // CTAs per rank of the dense all-reduce kernel
-  // symmetric block: dense gradient vector | 4 flag arrays [world][kCommMaxCtas] (dense round 1, 2; sparse round 1, 2)
+  // symmetric block: dense gradient vector | 4 flag arrays [world][kCommMaxCtas] (dense round 1, 2; sparse round 2; spare)
   // | inbox counts [world][kCommMaxCtas] | inbox gradients [world][cap][Ke] fp32 | inbox tails [world][cap]{gw, id}
+  // | (id, sender) index | arrival counter
   size_t off_dP, off_flags, off_in_count, off_in_grads, off_in_tails;
+  size_t off_entries;                // [V + world] u64 {epoch, slot + 1}: the record sender s pushed for an id this rank owns,
+                                     // at index id - rank + s; written by the SENDER, stale epochs are ignored, never cleared
+  size_t off_counter;                // u64 arrivals of the sparse exchange's first barrier (all CTAs of all ranks)
+  unsigned int epoch_base;           // StepState::comm_epoch when the views were attached (arrivals are counted from there)
   size_t flags_bytes;                // one flag array
   long long watchdog;                // clock64 ticks a cross-GPU or grid wait may take before the kernel traps
   int exact;                         // dense_exact table update: the owner publishes summed gradient rows, not parameters
@@ -316,8 +321,7 @@ struct XchgArgs {
   CommView cv;
   SparseArgs a;
   DenseArgs d;
-  unsigned long long* entry_of;          // [V + world] {epoch, slot+1} of the record sender r pushed for an owned id
-  unsigned int* grid_bar;
+  unsigned int* bar_local;               // {arrival counter, gate} x 2: this rank's side of the sparse kernel's two barriers
   OptHyper hyper;
 };
 int launch_dense_sync(const XchgArgs&, const XchgArgs* emu, int emu_ranks, cudaStream_t);
