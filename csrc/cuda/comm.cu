@@ -22,17 +22,17 @@
 //   phase 0  the row with id belongs to rank id % N.  dedupe already grouped my distinct ids by owner (segment o of
 //            the slot space), so I stream segment o -- gradient rows in fp32, {first-order gradient, id} tails -- into
 //            the inbox rank o keeps for me: 1/N of an all-gather's bytes, each record crosses NVLink once.
-//   barrier  CTA b <-> CTA b of the peers (both sides map records to CTAs the same way, so no grid-wide sync is
-//            needed before the signal)
-//   phase 1  index the records I received by (id, sender); grid barrier on this GPU
+//            The sender also writes the owner's (id, sender) index entry, stamped with the step's epoch.
+//   barrier  all CTAs of all ranks, hierarchical: the CTAs of a rank meet at a local counter, CTA 0 alone signals the
+//            peers (one system-scope release, cumulative over what the local CTAs wrote) and opens a local gate
 //   phase 2  for every received record whose sender is the lowest-ranked sender of its id: add the senders' rows in
 //            rank order, scale by 1/N, add the row's L2 term, apply the lazy optimizer to MY copy of the slots
 //            (m, v of a row live on its owner only), and store the new parameter row into every replica.
 //            HBM read-modify-write per GPU is union/N rows instead of the whole union.
-//   barrier  every replica has every row before the next step's gather starts.
+//   barrier  (same kind) every replica has every row before the next step's gather starts.
 //
-// Deadlock safety: a CTA only ever waits for its namesakes on the other ranks, every rank launches the same grids
-// in the same stream order, the sparse kernel's grid is at most one CTA per SM (its grid barrier needs them
+// Deadlock safety: every rank launches the same grids in the same stream order, the dense kernel's CTAs only wait for
+// their namesakes on the other ranks, the sparse kernel's grid is at most one CTA per SM (its barriers need them
 // co-resident), and every spin is bounded by a watchdog that traps instead of hanging.
 //
 // With kEmu the same kernels run N virtual ranks on ONE GPU as a single cooperative launch (blockIdx.x / ctas = rank):
