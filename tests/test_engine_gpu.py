@@ -463,3 +463,34 @@ def test_gradients_elementwise_and_against_the_unrounded_oracle():
             ref_sel, got_sel = ref, got[name]
         assert _rel(got_sel, ref_sel) < 1e-1, name
     eng.close()
+
+
+def test_partial_batch_between_graph_replays():
+    """Trainer.train_batch with fewer rows than batch_size goes through plain launches, which rewrite the
+    device-side row count the captured graph reads.  The count must be back to the full batch for the next replay, and
+    the partial step's loss is averaged over its own rows."""
+    from deepfm_b200.data.loader import HostBatch, alloc_slab
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.runtime.trainer import Trainer, TrainerOptions
+    B, F, V = 256, 39, 5000
+    cfg = DeepFMConfig(F, V, 32, (128, 64), (1.0, 1.0), l2_reg=0.0)
+    g = torch.Generator().manual_seed(3)
+    slab, ids, vals, labels = alloc_slab(B, F, torch.int32, pin_memory=True)
+    ids.copy_(torch.randint(1, V, (B, F), generator=g, dtype=torch.int32))
+    vals.copy_(torch.rand(B, F, generator=g)); labels.copy_((torch.rand(B, generator=g) < 0.3).float())
+    tr = Trainer(cfg, TrainerOptions(batch_size=B, optimizer="GD", learning_rate=0.0, backend="fused", seed=5,
+                                     cuda_graph=True), device=torch.device("cuda", 0), init_model=DeepFM(cfg, seed=11))
+    tr.train_step_host(slab)
+    full = tr.last_loss(wait_current=True)
+    n = 100
+    tr.train_batch(HostBatch(ids[:n].clone(), vals[:n].clone(), labels[:n].clone(), n))
+    part = tr.last_loss(wait_current=True)
+    assert tr.engine.read_state()["count"] == B                      # restored for the graph
+    m = tr.export_model()
+    with torch.no_grad():
+        ref_part = float(m.data_loss(m(ids[:n].long(), vals[:n]), labels[:n]))
+    assert abs(part - ref_part) < 2e-2 * abs(ref_part) + 1e-3        # mean over the 100 rows, not over 256
+    tr.train_step_host(slab)                                         # weights are frozen (lr 0): same batch, same loss
+    again = tr.last_loss(wait_current=True)
+    assert abs(again - full) < 1e-5 * abs(full) + 1e-6
+    tr.close()
