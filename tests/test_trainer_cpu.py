@@ -196,3 +196,40 @@ def test_train_batches_consumes_every_batch_once_in_order(tmp_path):
         with torch.no_grad():
             want.append(float(init.data_loss(init(ids, vals), labels)))
     np.testing.assert_allclose(got, want, rtol=1e-5)
+
+
+def _gather_proc(rank, world, port, out_dir):
+    import os
+    import types
+    import torch
+    import torch.distributed as dist
+    from deepfm_b200.parallel.sync_dp import gather_owner_sharded_slots
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    V, K = 23, 4
+    # every rank holds current values only in the rows it owns (id % world == rank); the rest is stale (-1)
+    def shard(shape_tail):
+        t = torch.full((V,) + shape_tail, -1.0)
+        own = torch.arange(V) % world == rank
+        t[own] = torch.arange(V, dtype=torch.float32)[own].view(-1, *([1] * len(shape_tail))) * (1.0 if not shape_tail else torch.ones(shape_tail))
+        return t
+    eng = types.SimpleNamespace(table_update_mode="lazy", fm_w_s0=shard(()), fm_w_s1=shard(()) * 2, fm_v_s0=shard((K,)),
+                                fm_v_s1=shard((K,)) * 3)
+    gather_owner_sharded_slots(eng)
+    torch.save({"w0": eng.fm_w_s0, "w1": eng.fm_w_s1, "v0": eng.fm_v_s0, "v1": eng.fm_v_s1}, os.path.join(out_dir, f"g{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_owner_sharded_slots_are_gathered_before_a_checkpoint(tmp_path):
+    """Multi-GPU lazy update keeps the optimizer slots of row id on rank id % world; before a checkpoint every rank must
+    end up with every row (parallel/sync_dp.gather_owner_sharded_slots) -- here over gloo with three ranks."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    mp.spawn(_gather_proc, args=(3, port, str(tmp_path)), nprocs=3, join=True)
+    ref = torch.arange(23, dtype=torch.float32)
+    for r in range(3):
+        g = torch.load(tmp_path / f"g{r}.pt")
+        assert torch.equal(g["w0"], ref) and torch.equal(g["w1"], 2 * ref)
+        assert torch.equal(g["v0"], ref[:, None].expand(23, 4)) and torch.equal(g["v1"], 3 * ref[:, None].expand(23, 4))
