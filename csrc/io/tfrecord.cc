@@ -394,9 +394,23 @@ int read_int64_list(const uint8_t* p, const uint8_t* end, T* out, int cap, uint6
       if (!get_len(p, end, e)) return -1;
       while (p < e) {
         uint64_t v;
-        // fast path: 1- and 2-byte varints cover every id < 16384; the rest go the slow way
-        if (*p < 0x80) {
-          v = *p++;
+        // fast paths: 1-, 2- and 3-byte varints cover every id < 2^21 (Criteo-sized vocabularies); the rest go the
+        // general way.  The three-byte read stays inside the list (p + 3 <= e) or falls through.
+        const uint32_t b0 = p[0];
+        if (b0 < 0x80) {
+          v = b0;
+          p += 1;
+        } else if (e - p >= 3) {
+          const uint32_t b1 = p[1], b2 = p[2];
+          if (b1 < 0x80) {
+            v = (b0 & 0x7f) | (b1 << 7);
+            p += 2;
+          } else if (b2 < 0x80) {
+            v = (b0 & 0x7f) | ((b1 & 0x7f) << 7) | (b2 << 14);
+            p += 3;
+          } else if (!get_varint(p, e, v)) {
+            return -1;
+          }
         } else if (!get_varint(p, e, v)) {
           return -1;
         }
