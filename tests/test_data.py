@@ -292,3 +292,100 @@ def test_loader_can_be_closed_mid_stream(tmp_path):
             if i == it % 5:
                 break
         ld.close()
+
+
+# ---------------------------------------------------------------- fast paths of the codec (canonical layout, SIMD id runs)
+def _crc32c_bitwise(data: bytes) -> int:
+    c = 0xFFFFFFFF
+    for b in data:
+        c ^= b
+        for _ in range(8):
+            c = (c >> 1) ^ (0x82F63B78 & -(c & 1))
+    return c ^ 0xFFFFFFFF
+
+
+def test_crc32c_three_lane_joins_match_bitwise_definition():
+    """Every length class of the interleaved CRC (3 x 1024 / 256 / 96 / 32 byte lanes, 8-byte words, byte tail), at
+    every alignment of the first byte."""
+    rng = np.random.default_rng(5)
+    blob = rng.integers(0, 256, 8200, dtype=np.uint8).tobytes()
+    lengths = [0, 1, 7, 8, 9, 95, 96, 97, 287, 288, 289, 297, 298, 299, 767, 768, 769, 1000, 3071, 3072, 3073, 3500,
+               4096, 7000, 8190]
+    for n in lengths:
+        for off in (0, 1, 3, 5, 7):
+            assert T.crc32c(blob[off:off + n]) == _crc32c_bitwise(blob[off:off + n]), (n, off)
+
+
+_ID_CLASSES = [(0, 128), (128, 16384), (16384, 2 ** 21), (2 ** 21, 2 ** 28), (2 ** 40, 2 ** 62)]
+
+
+@settings(max_examples=400, deadline=None)
+@given(n=st.integers(1, 80), seed=st.integers(0, 2 ** 31), wide=st.booleans(), i32=st.booleans(),
+       run=st.sampled_from([0, 1, 2, 3]))
+def test_example_fast_path_matches_input_for_mixed_varint_widths(n, seed, wide, i32, run):
+    """The canonical-layout decoder takes ids in steps of four when it sees a run of one- or three-byte varints and one
+    at a time otherwise; ids of four bytes and more send the record to the generic walker.  Any mix must round-trip."""
+    rng = np.random.default_rng(seed)
+    top = len(_ID_CLASSES) if (wide and not i32) else (4 if wide else 3)
+    if run == 0:       # every id its own width
+        cls = rng.integers(0, top, n)
+    elif run == 1:     # Criteo shape: a prefix of small ids, then large ones
+        k = int(rng.integers(0, n + 1))
+        cls = np.concatenate([np.zeros(k, np.int64), np.full(n - k, 2)])
+    elif run == 2:     # long runs with one odd id somewhere
+        cls = np.full(n, int(rng.integers(0, 3)))
+        cls[int(rng.integers(0, n))] = int(rng.integers(0, top))
+    else:              # all three-byte
+        cls = np.full(n, 2)
+    ids = np.array([int(rng.integers(*_ID_CLASSES[c])) for c in cls], dtype=np.int64)
+    vals = rng.standard_normal(n).astype(np.float32)
+    payload = T.encode_example(0.25, ids, vals, packed=True)
+    lab, i2, v2 = T.parse_example(payload, n, ids_dtype=np.int32 if i32 else np.int64)
+    assert lab == np.float32(0.25) and (i2 == ids).all() and (v2 == vals).all()
+    assert i2.dtype == (np.int32 if i32 else np.int64)
+
+
+def test_canonical_and_generic_decoders_agree_on_reordered_and_padded_records():
+    """A record the fast path declines (unknown extra key, unpacked lists) must decode to the same arrays."""
+    rng = np.random.default_rng(11)
+    ids = np.concatenate([np.arange(1, 14), rng.integers(16384, 117581, 26)])
+    vals = rng.random(39).astype(np.float32)
+    canon = T.encode_example(1.0, ids, vals, packed=True)
+    lab, i1, v1 = T.parse_example(canon, 39, ids_dtype=np.int32)
+    for other in (T.encode_example(1.0, ids, vals, packed=False),
+                  _with_extra_entry(canon)):
+        lab2, i2, v2 = T.parse_example(other, 39, ids_dtype=np.int32)
+        assert lab2 == lab and (i2 == i1).all() and (v2 == v1).all()
+    assert (i1 == ids).all()
+
+
+def _with_extra_entry(payload: bytes) -> bytes:
+    """Example{features{... + entry{key 'zz', value Feature{bytes_list{'x'}}}}}"""
+    assert payload[0] == 0x0A
+    body = payload[2:] if payload[1] < 0x80 else payload[3:]
+    extra = bytes([0x0A, 0x0B, 0x0A, 0x02]) + b"zz" + bytes([0x12, 0x05, 0x0A, 0x03, 0x0A, 0x01]) + b"x"
+    body = body + extra
+    n = len(body)
+    return bytes([0x0A, (n & 0x7F) | 0x80, n >> 7]) + body if n >= 128 else bytes([0x0A, n]) + body
+
+
+def test_loader_range_check_inside_a_vector_step(tmp_path):
+    """One id of a three-byte run is out of range: the loader names it exactly (the vector step declines, the generic
+    walker reports)."""
+    from deepfm_b200.data.tfrecord import DataError
+    path = str(tmp_path / "tr.tfrecords")
+    rng = np.random.default_rng(2)
+    with T.TFRecordWriter(path) as w:
+        for r in range(64):
+            ids = np.concatenate([np.arange(1, 14), rng.integers(20000, 90000, 26)])
+            if r == 40:
+                ids[22] = 99999
+            w.write_example(float(r & 1), ids, np.ones(39, np.float32))
+    ok = BatchLoader([path], 39, 16, feature_size=100000, ids_dtype=torch.int32, num_workers=2)
+    assert sum(hb.count for hb in ok) == 64
+    ok.close()
+    bad = BatchLoader([path], 39, 16, feature_size=99999, ids_dtype=torch.int32, num_workers=2)
+    with pytest.raises(DataError, match=r"feature id 99999 is outside \[0, feature_size = 99999\)"):
+        for _ in bad:
+            pass
+    bad.close()
