@@ -155,13 +155,18 @@ class MappedSource final : public RecordSource {
 
 }  // namespace
 
+// CRC32C of the eight bytes of a length field: one instruction, no call
+static inline uint32_t crc32c_u64(uint64_t v) {
+  return static_cast<uint32_t>(_mm_crc32_u64(0xffffffffu, v)) ^ 0xffffffffu;
+}
+
 static inline bool header_ok(const uint8_t* base, size_t size, size_t pos, uint64_t* n) {
   if (size - pos < 16) return false;
   uint32_t lcrc;
   memcpy(n, base + pos, 8);
   memcpy(&lcrc, base + pos + 8, 4);
   if (*n > size - pos - 16) return false;
-  return mask_crc(crc32c(base + pos, 8)) == lcrc;
+  return mask_crc(crc32c_u64(*n)) == lcrc;
 }
 
 size_t find_record_start(const uint8_t* base, size_t size, size_t from, size_t to) {
@@ -186,7 +191,7 @@ size_t walk_framing(const uint8_t* base, size_t size, size_t pos, size_t limit_s
     if (verify_len_crc) {
       uint32_t lcrc;
       memcpy(&lcrc, base + pos + 8, 4);
-      if (mask_crc(crc32c(base + pos, 8)) != lcrc) {
+      if (mask_crc(crc32c_u64(n)) != lcrc) {
         set_error("%s: corrupt length CRC at offset %zu", path, pos);
         return static_cast<size_t>(-1);
       }
@@ -196,6 +201,16 @@ size_t walk_framing(const uint8_t* base, size_t size, size_t pos, size_t limit_s
       return static_cast<size_t>(-1);
     }
     out->push_back(RecSpan{pos + 12, static_cast<uint32_t>(n)});
+    // The walk is a pointer chase -- the place of the next header is known only once this one has arrived -- and it
+    // touches one cache line in five, which no hardware prefetcher follows: left alone it pays one DRAM latency per
+    // record.  Records of one dataset are nearly the same size, so the header kAhead records on lies within a line
+    // or two of pos + kAhead * (this record's size): ask for those lines now.
+    constexpr size_t kAhead = 12;
+    const size_t guess = pos + kAhead * (n + 16);
+    if (guess + 64 <= size) {
+      __builtin_prefetch(base + guess - 32);
+      __builtin_prefetch(base + guess + 32);
+    }
     pos += 12 + n + 4;
   }
   return pos;
