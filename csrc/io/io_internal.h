@@ -5,6 +5,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <nmmintrin.h>
 #include <memory>
 #include <string>
 #include <vector>
@@ -17,6 +18,8 @@ void set_error(const char* fmt, ...);
 
 uint32_t crc32c(const void* data, size_t n);
 inline uint32_t mask_crc(uint32_t c) { return ((c >> 15) | (c << 17)) + 0xa282ead8u; }
+// CRC32C of the eight bytes of a record's length field (little endian): one instruction, no call
+inline uint32_t crc32c_u64(uint64_t v) { return static_cast<uint32_t>(_mm_crc32_u64(0xffffffffu, v)) ^ 0xffffffffu; }
 
 // ---------------------------------------------------------------------------
 // Record sources.  next() yields a pointer valid until the following next()
@@ -31,6 +34,9 @@ class RecordSource {
   virtual uint64_t bytes_consumed() const = 0;
   // mapped files only: the whole file as one byte range (lets several threads walk the framing of disjoint ranges)
   virtual bool mapping(const uint8_t** base, size_t* size) const { return false; }
+  // streams only: the descriptor, for a reader that takes the bytes in large blocks itself (the batch loader does;
+  // it must then never call next()).  -1 for everything else.
+  virtual int raw_fd() const { return -1; }
 };
 
 // Walks the TFRecord framing of base[pos, limit_start) (records that START before limit_start): appends

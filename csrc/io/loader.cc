@@ -7,13 +7,19 @@
 //                   consecutive length CRCs that check out) and the batcher confirms it against the true chain --
 //                   the previous range's end -- re-walking the range itself on the rare false guess
 //   batcher thread  consumes the ranges in order, applies the record-level shard (index % n == i), groups kept
-//                   records into batches and hands each batch to the workers in row ranges; FIFOs / stdin
-//                   (SageMaker pipe mode) are read sequentially by this thread instead
-//   parse tasks     verify CRCs + decode Examples straight into the caller's (pinned) slot, check the id range
+//                   records into batches and hands each batch to the workers in row ranges.  FIFOs / stdin
+//                   (SageMaker pipe mode) cannot be indexed ahead: this thread reads them in 4 MiB blocks, checks
+//                   the length fields and cuts the block into records IN PLACE -- the batch keeps the block alive,
+//                   nothing is copied after read(2), and the payload CRCs are left to the workers
+//   parse tasks     verify payload CRCs + decode Examples straight into the caller's (pinned) slot, check the id
+//                   range
 //   consumer        dfio_loader_next() returns slots strictly in stream order
 //
 // Slots form a ring: batch b lives in slot b % num_slots, so "prefetch depth" is
 // num_slots - 1 and the consumer's release() is what lets the batcher run ahead.
+#include <errno.h>
+#include <unistd.h>
+
 #include <atomic>
 #include <condition_variable>
 #include <deque>
@@ -25,29 +31,35 @@
 namespace dfio {
 namespace {
 
-constexpr uint64_t kNoOffset = ~0ull;
 constexpr size_t kIndexChunk = 1u << 20;
+constexpr size_t kStreamBlock = 4u << 20;
+constexpr uint64_t kMaxStreamRecord = 1ull << 31;
 
 struct Rec {
-  const uint8_t* p;   // payload (resolved from `off` once the arena is final)
+  const uint8_t* p;   // payload; the record's 4-byte payload CRC follows it
   uint32_t len;
-  uint32_t seg;       // index into BatchWork::segs (which file the record came from)
-  uint64_t off;       // payload offset inside BatchWork::arena, or kNoOffset for mapped records
+  uint32_t seg;       // index into BatchWork::segs (what the record points into)
 };
 
+// What the records of a batch point into: a mapped file, or one block of a stream.
 struct FileSeg {
-  std::shared_ptr<RecordSource> src;   // keeps a mapping alive while the batch points into it
-  const uint8_t* base = nullptr;       // mapped files: start of the mapping (for error offsets)
+  std::shared_ptr<const void> keep;    // the mapping / the block: alive while the batch points into it
+  const uint8_t* base = nullptr;       // its first byte ...
+  uint64_t base_off = 0;               // ... and where that byte sits in the file or stream (for error messages)
   std::string path;
 };
 
-// One batch worth of records.  For mapped files the records point into the
-// mapping (kept alive by `segs`); for streams they point into `arena`.
+// A stretch of a stream as read(2) delivered it; recycled through Loader::free_blocks_ so its pages stay resident.
+struct StreamBlock {
+  std::vector<uint8_t> buf;
+  uint64_t stream_off = 0;             // stream position of buf[0]
+};
+
+// One batch worth of records (they point into what `segs` keeps alive).
 struct BatchWork {
   int slot = 0;
   int count = 0;
   std::vector<Rec> recs;
-  std::vector<uint8_t> arena;
   std::vector<FileSeg> segs;
   std::atomic<int> remaining{0};
 };
@@ -105,6 +117,8 @@ class Loader {
     cv_chunk_.notify_all();
     if (reader_.joinable()) reader_.join();
     for (auto& w : workers_) w.join();
+    parse_tasks_.clear();        // batches still queued give their stream blocks back while the pool exists
+    index_tasks_.clear();
   }
 
   int next(int* slot, int* count) {
@@ -203,10 +217,11 @@ class Loader {
     es.bw->recs.reserve(cfg_.batch_size);
   }
 
-  // the batch's reference to the file the next records come from
-  uint32_t seg_of(EpochState& es, const std::shared_ptr<RecordSource>& src, const uint8_t* base, const std::string& path) {
+  // the batch's reference to the mapping / block the next records lie in
+  uint32_t seg_of(EpochState& es, const std::shared_ptr<const void>& keep, const uint8_t* base, uint64_t base_off,
+                  const std::string& path) {
     auto& segs = es.bw->segs;
-    if (segs.empty() || segs.back().src != src) segs.push_back(FileSeg{src, base, path});
+    if (segs.empty() || segs.back().keep != keep) segs.push_back(FileSeg{keep, base, base_off, path});
     return static_cast<uint32_t>(segs.size() - 1);
   }
 
@@ -237,6 +252,7 @@ class Loader {
     const size_t n_chunks = (size + kIndexChunk - 1) / kIndexChunk;
     const size_t window = static_cast<size_t>(std::max(2, cfg_.num_workers));
     std::deque<std::shared_ptr<Chunk>> inflight;
+    const std::shared_ptr<const void> keep = src;
     size_t next_chunk = 0, expected = 0;      // `expected` = true start of the next record (the chain)
     for (size_t ci = 0; ci < n_chunks; ++ci) {
       while (next_chunk < n_chunks && inflight.size() < window) {
@@ -278,28 +294,92 @@ class Loader {
       expected = std::max(expected, c->stop);
       for (const RecSpan& r : c->recs) {
         if (es.idx++ % cfg_.shard_n != cfg_.shard_i) continue;
-        if (!add_record(es, Rec{base + r.off, r.len, seg_of(es, src, base, path), kNoOffset})) return false;
+        if (!add_record(es, Rec{base + r.off, r.len, seg_of(es, keep, base, 0, path)})) return false;
       }
     }
     bytes_ += static_cast<int64_t>(size);
     return true;
   }
 
-  // FIFO / stdin: sequential; payloads are copied (their CRCs were checked by the stream source)
-  bool read_stream(EpochState& es, const std::shared_ptr<RecordSource>& src, const std::string& path) {
-    const uint8_t* d;
-    uint64_t n;
-    int r;
-    while ((r = src->next(&d, &n)) == 1) {
-      if (es.idx++ % cfg_.shard_n != cfg_.shard_i) continue;
-      const size_t off = es.bw->arena.size();
-      es.bw->arena.insert(es.bw->arena.end(), d, d + n);
-      if (!add_record(es, Rec{nullptr, static_cast<uint32_t>(n), seg_of(es, src, nullptr, path), off})) return false;
-      // (stop / failure are noticed in submit(), once per batch: no lock per record on this path)
+  // ---- streams ----------------------------------------------------------------------------------
+  std::shared_ptr<StreamBlock> get_block(size_t cap) {
+    std::unique_ptr<StreamBlock> b;
+    {
+      std::lock_guard<std::mutex> l(pool_mu_);
+      if (!free_blocks_.empty()) {
+        b = std::move(free_blocks_.back());
+        free_blocks_.pop_back();
+      }
     }
-    bytes_ += static_cast<int64_t>(src->bytes_consumed());
-    if (r < 0) {
-      fail(dfio_last_error());
+    if (!b) b = std::make_unique<StreamBlock>();
+    if (b->buf.size() < cap) b->buf.resize(cap);
+    return std::shared_ptr<StreamBlock>(b.release(), [this](StreamBlock* x) {
+      std::lock_guard<std::mutex> l(pool_mu_);
+      if (free_blocks_.size() < 16) free_blocks_.emplace_back(x);
+      else delete x;
+    });
+  }
+
+  // FIFO / stdin: read in blocks, cut into records in place.  A record that straddles the end of a block is carried
+  // to the front of the next one (a record larger than a block gets a block of its own size).
+  bool read_stream(EpochState& es, int fd, const std::string& path) {
+    const bool verify = cfg_.verify_crc != 0;
+    std::shared_ptr<StreamBlock> blk = get_block(kStreamBlock);
+    std::shared_ptr<const void> keep = blk;
+    blk->stream_off = 0;
+    size_t fill = 0, pos = 0;       // bytes of the block that hold data / that are already cut into records
+    uint64_t total = 0;
+    for (bool eof = false; !eof;) {
+      if (fill == blk->buf.size()) {
+        const size_t tail = fill - pos;
+        size_t need = kStreamBlock;
+        if (tail >= 12) {           // its length field passed the checks below when it was first seen
+          uint64_t n;
+          memcpy(&n, blk->buf.data() + pos, 8);
+          need = std::max<size_t>(need, n + 16);
+        }
+        std::shared_ptr<StreamBlock> nb = get_block(need);
+        memcpy(nb->buf.data(), blk->buf.data() + pos, tail);
+        nb->stream_off = blk->stream_off + pos;
+        blk = std::move(nb);
+        keep = blk;
+        fill = tail;
+        pos = 0;
+      }
+      const ssize_t r = ::read(fd, blk->buf.data() + fill, blk->buf.size() - fill);
+      if (r < 0) {
+        if (errno == EINTR) continue;
+        fail(path + ": read failed: " + strerror(errno));
+        return false;
+      }
+      eof = r == 0;
+      fill += static_cast<size_t>(r);
+      total += static_cast<uint64_t>(r);
+      const uint8_t* b = blk->buf.data();
+      while (fill - pos >= 12) {
+        uint64_t n;
+        uint32_t lcrc;
+        memcpy(&n, b + pos, 8);
+        memcpy(&lcrc, b + pos + 8, 4);
+        if (verify && mask_crc(crc32c_u64(n)) != lcrc) {
+          fail(path + ": corrupt length CRC at stream offset " + std::to_string(blk->stream_off + pos));
+          return false;
+        }
+        if (n > kMaxStreamRecord) {
+          fail(path + ": implausible record length " + std::to_string(n) + " at stream offset " +
+               std::to_string(blk->stream_off + pos));
+          return false;
+        }
+        if (fill - pos < 16 + n) break;     // the rest of it has not arrived yet
+        if (es.idx++ % cfg_.shard_n == cfg_.shard_i &&
+            !add_record(es, Rec{b + pos + 12, static_cast<uint32_t>(n), seg_of(es, keep, b, blk->stream_off, path)}))
+          return false;
+        pos += 16 + n;
+      }
+    }
+    bytes_ += static_cast<int64_t>(total);
+    if (pos != fill) {
+      fail(path + ": stream ends inside a record (stream offset " + std::to_string(blk->stream_off + pos) + ")");
       return false;
     }
     return true;
@@ -318,7 +398,14 @@ class Loader {
         }
         const uint8_t* base = nullptr;
         size_t size = 0;
-        const bool ok = src->mapping(&base, &size) ? read_mapped(es, src, base, size, path) : read_stream(es, src, path);
+        bool ok;
+        if (src->mapping(&base, &size)) {
+          ok = read_mapped(es, src, base, size, path);
+        } else {
+          const int fd = src->raw_fd();      // `src` owns the descriptor; the loader takes the bytes itself
+          ok = fd >= 0 && read_stream(es, fd, path);
+          if (fd < 0) fail(path + ": not a mapped file and not a readable stream");
+        }
         if (!ok) return;
       }
       if (!es.bw->recs.empty() && !cfg_.drop_remainder) {
@@ -334,9 +421,6 @@ class Loader {
 
   bool finish_and_submit(std::shared_ptr<BatchWork>& bw) {
     bw->count = static_cast<int>(bw->recs.size());
-    const uint8_t* base = bw->arena.data();
-    for (auto& r : bw->recs)
-      if (r.off != kNoOffset) r.p = base + r.off;
     return submit(bw);
   }
 
@@ -344,7 +428,8 @@ class Loader {
   std::string where(const BatchWork& bw, const Rec& rec) const {
     const FileSeg& sg = bw.segs[rec.seg];
     char buf[64] = "";
-    if (sg.base) snprintf(buf, sizeof(buf), ", record payload at byte offset %llu", (unsigned long long)(rec.p - sg.base));
+    if (sg.base)
+      snprintf(buf, sizeof(buf), ", record payload at byte offset %llu", (unsigned long long)(sg.base_off + (rec.p - sg.base)));
     return " (" + sg.path + buf + ")";
   }
 
@@ -375,7 +460,7 @@ class Loader {
       bool ok = true;
       for (int r = t.row0; r < t.row1 && ok; ++r) {
         const Rec& rec = t.bw->recs[r];
-        if (cfg_.verify_crc && rec.off == kNoOffset) {  // mapped record: framing sits around the payload
+        if (cfg_.verify_crc) {      // the framing sits around the payload, in a mapping and in a stream block alike
           uint32_t dcrc;
           memcpy(&dcrc, rec.p + rec.len, 4);
           if (mask_crc(crc32c(rec.p, rec.len)) != dcrc) {
@@ -405,6 +490,8 @@ class Loader {
 
   dfio_loader_config cfg_;
   std::vector<std::string> paths_;
+  std::mutex pool_mu_;                                        // declared first: blocks come back here while the
+  std::vector<std::unique_ptr<StreamBlock>> free_blocks_;     // members below are being destroyed
   std::vector<Slot> slots_;
   std::mutex mu_;
   std::condition_variable cv_slot_, cv_task_, cv_ready_, cv_chunk_;

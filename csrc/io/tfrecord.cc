@@ -155,11 +155,6 @@ class MappedSource final : public RecordSource {
 
 }  // namespace
 
-// CRC32C of the eight bytes of a length field: one instruction, no call
-static inline uint32_t crc32c_u64(uint64_t v) {
-  return static_cast<uint32_t>(_mm_crc32_u64(0xffffffffu, v)) ^ 0xffffffffu;
-}
-
 static inline bool header_ok(const uint8_t* base, size_t size, size_t pos, uint64_t* n) {
   if (size - pos < 16) return false;
   uint32_t lcrc;
@@ -264,6 +259,7 @@ class StreamSource final : public RecordSource {
   }
   bool stable_pointers() const override { return false; }
   uint64_t bytes_consumed() const override { return consumed_; }
+  int raw_fd() const override { return lo_ == hi_ && consumed_ == 0 ? fd_ : -1; }
 
  private:
   // 1 = ok, 0 = clean EOF before any byte (only if eof_ok), -1 = error

@@ -389,3 +389,90 @@ def test_loader_range_check_inside_a_vector_step(tmp_path):
         for _ in bad:
             pass
     bad.close()
+
+
+# ---------------------------------------------------------------- streams: blocks cut into records in place
+def _all_batches(loader):
+    out = []
+    for hb in loader:
+        out.append((hb.feat_ids.clone(), hb.feat_vals.clone(), hb.labels.clone()))
+    loader.close()
+    return out
+
+
+def test_stream_blocks_deliver_what_the_mapped_reader_delivers(tmp_path):
+    """A stream is read in 4 MiB blocks; records that straddle a block boundary are carried over.  10 MB of records,
+    fed through a FIFO in writes of odd sizes, must come out exactly like the mapped file: every shard, two epochs
+    of the file-backed stream."""
+    from deepfm_b200.data.tfrecord import generate_synthetic
+    path, fifo = str(tmp_path / "tr.tfrecords"), str(tmp_path / "training_0")
+    generate_synthetic(path, 33000, 39, 117581, n_dense=13, seed=9, pos_rate=0.25, zipf_s=1.05)
+    assert os.path.getsize(path) > 2 * (4 << 20)
+    for shard_n, shard_i in ((1, 0), (3, 2)):
+        kw = dict(shard_n=shard_n, shard_i=shard_i, ids_dtype=torch.int32, num_workers=3, drop_remainder=False,
+                  feature_size=117581)
+        want = _all_batches(BatchLoader([path], 39, 500, **kw))
+        os.mkfifo(fifo)
+
+        def feed():
+            data, rng, pos = open(path, "rb").read(), np.random.default_rng(1), 0
+            with open(fifo, "wb", buffering=0) as f:
+                while pos < len(data):
+                    n = int(rng.integers(1, 300000))
+                    f.write(data[pos:pos + n])
+                    pos += n
+
+        t = threading.Thread(target=feed)
+        t.start()
+        got = _all_batches(BatchLoader([fifo], 39, 500, streaming=True, **kw))
+        t.join()
+        os.unlink(fifo)
+        assert len(got) == len(want)
+        for g, w in zip(got, want):
+            assert all(torch.equal(a, b) for a, b in zip(g, w))
+    # a regular file forced into stream mode, two epochs
+    want2 = _all_batches(BatchLoader([path], 39, 512, num_epochs=2, ids_dtype=torch.int32))
+    got2 = _all_batches(BatchLoader([path], 39, 512, num_epochs=2, ids_dtype=torch.int32, streaming=True))
+    assert len(got2) == len(want2) == 2 * (33000 // 512)
+    assert all(torch.equal(g[0], w[0]) and torch.equal(g[2], w[2]) for g, w in zip(got2, want2))
+
+
+def test_stream_record_larger_than_a_block(tmp_path):
+    """One Example of 700k fields is ~6 MB: larger than a stream block, so it gets a block of its own size."""
+    F = 700_000
+    path = str(tmp_path / "big.tfrecords")
+    rng = np.random.default_rng(4)
+    ids = rng.integers(0, 100000, F)
+    vals = rng.random(F).astype(np.float32)
+    with T.TFRecordWriter(path) as w:
+        w.write_example(1.0, np.arange(F) % 7, np.ones(F, np.float32))
+        w.write_example(0.0, ids, vals)
+        w.write_example(1.0, np.arange(F) % 5, np.ones(F, np.float32))
+    assert os.path.getsize(path) > 2 * (4 << 20) and len(T.encode_example(0.0, ids, vals)) > (4 << 20)
+    got = _all_batches(BatchLoader([path], F, 1, streaming=True, ids_dtype=torch.int64, num_workers=2, num_slots=2))
+    assert len(got) == 3
+    assert (got[1][0][0].numpy() == ids).all() and (got[1][1][0].numpy() == vals).all() and got[1][2].item() == 0.0
+    assert (got[2][0][0].numpy() == np.arange(F) % 5).all()
+
+
+def test_stream_errors_name_the_offset(tmp_path):
+    src = str(tmp_path / "src.tfrecords")
+    with T.TFRecordWriter(src) as w:
+        for i in range(50):
+            w.write_example(float(i & 1), np.arange(4) + i, np.ones(4, np.float32))
+    data = open(src, "rb").read()
+    rec = len(data) // 50
+    cases = {
+        "payload": (bytearray(data), 20 * rec + 30, r"CRC mismatch.*byte offset %d\b" % (20 * rec + 12)),
+        "length": (bytearray(data), 10 * rec + 2, r"corrupt length CRC at stream offset %d\b" % (10 * rec)),
+    }
+    for name, (buf, at, pattern) in cases.items():
+        buf[at] ^= 0x40
+        f = str(tmp_path / f"{name}.tfrecords")
+        open(f, "wb").write(bytes(buf))
+        with pytest.raises(T.DataError, match=pattern):
+            list(BatchLoader([f], 4, 5, streaming=True))
+    f = str(tmp_path / "cut.tfrecords")
+    open(f, "wb").write(data[: 30 * rec + 7])
+    with pytest.raises(T.DataError, match=r"stream ends inside a record \(stream offset %d\)" % (30 * rec)):
+        list(BatchLoader([f], 4, 5, streaming=True))
