@@ -129,21 +129,38 @@ def pool_path(batch: int, pool: int, rank: int) -> str:
     return os.path.join(tempfile.gettempdir(), f"dfm_bench_r{rank}_{n}_{FEATURE}.tfrecords")
 
 
+def thread_cpu_seconds():
+    """CPU seconds (user + system) of every thread of this process, by thread name."""
+    out = {}
+    try:
+        for tid in os.listdir("/proc/self/task"):
+            with open(f"/proc/self/task/{tid}/stat") as f:
+                st = f.read()
+            name = st[st.index("(") + 1:st.rindex(")")]
+            f_ = st[st.rindex(")") + 2:].split()
+            out[(tid, name)] = (int(f_[11]) + int(f_[12])) / os.sysconf("SC_CLK_TCK")
+    except (OSError, ValueError):
+        pass
+    return out
+
+
 def measure_pipeline(trainer, path: str, batch: int, seconds: float = 2.5):
     """TFRecord file -> native loader (framing, CRC, Example decode into pinned slabs) -> Trainer.train_batches ->
     loss on the host: what `python -m deepfm_b200.train` achieves per rank, input pipeline included."""
     import torch
     from deepfm_b200.data.loader import BatchLoader
-    workers = max(2, min(32, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 8)
+    workers = max(2, min(32, cores // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
     loader = BatchLoader([path], FIELD, batch, num_epochs=100000, drop_remainder=True, num_workers=workers, num_slots=8,
                          ids_dtype=torch.int32, verify_crc=True)
-    n, t0, loss = 0, None, float("nan")
+    n, t0, loss, cpu0 = 0, None, float("nan"), {}
     gen = trainer.train_batches(loader)
     try:
         for _ in gen:
             if t0 is None:                       # the first batch pays thread start-up; time from the second on
                 torch.cuda.synchronize()
                 t0 = time.time()
+                cpu0 = thread_cpu_seconds()
                 continue
             n += 1
             if n % 64 == 0:
@@ -151,11 +168,19 @@ def measure_pipeline(trainer, path: str, batch: int, seconds: float = 2.5):
                 if time.time() - t0 >= seconds:
                     break
     finally:
+        cpu1, t1 = thread_cpu_seconds(), time.time()
         gen.close()                              # gives the ring slots back before the loader goes away
         loader.close()
     torch.cuda.synchronize()
     dt = time.time() - t0
-    return n * batch / dt, dt, workers, loss
+    # where the host CPU went, in cores (CPU seconds per second of the window), by thread name
+    me = str(os.getpid())
+    use = {}
+    for key, v in cpu1.items():
+        name = "main" if key[0] == me else key[1]
+        use[name] = use.get(name, 0.0) + (v - cpu0.get(key, 0.0)) / max(t1 - t0, 1e-9)
+    cpu = {k: round(v, 2) for k, v in sorted(use.items(), key=lambda kv: -kv[1]) if v >= 0.01}
+    return n * batch / dt, dt, workers, loss, cpu, cores
 
 
 def make_host_pool(batch: int, pool: int, rank: int, world: int):
@@ -466,12 +491,13 @@ def main():
     # ---------------- input pipeline included: TFRecord file -> loader -> train_batches ----------------
     pipe = None
     if not args.no_pipeline:
-        rate, dt, workers, _ = measure_pipeline(trainer, pool_path(args.batch, args.pool, rank), args.batch)
+        rate, dt, workers, _, cpu_use, cores = measure_pipeline(trainer, pool_path(args.batch, args.pool, rank), args.batch)
         pr = torch.tensor([rate], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(pr, op=dist.ReduceOp.MIN)          # the job runs at the pace of its slowest rank
         pipe = {"value": float(pr.item()) * world, "unit": "examples/s", "seconds": round(dt, 2),
-                "parser_threads_per_rank": workers, "host_cores": os.cpu_count(),
+                "parser_threads_per_rank": workers, "host_cores": os.cpu_count(), "cores_this_rank_may_use": cores,
+                "rank0_cpu_cores_used_by_thread": cpu_use,
                 "what": "TFRecord file (page cache) -> framing + CRC32C + Example decode -> pinned slabs -> H2D -> step -> loss"}
 
     t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)

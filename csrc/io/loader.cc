@@ -18,6 +18,7 @@
 // Slots form a ring: batch b lives in slot b % num_slots, so "prefetch depth" is
 // num_slots - 1 and the consumer's release() is what lets the batcher run ahead.
 #include <errno.h>
+#include <pthread.h>
 #include <unistd.h>
 
 #include <atomic>
@@ -195,8 +196,9 @@ class Loader {
     slots_[s].count = bw->count;
     slots_[s].batch_no = produced_;
     bw->slot = s;
-    // split into row ranges so several workers share one batch
-    const int chunk = std::max(64, (bw->count + cfg_.num_workers - 1) / cfg_.num_workers);
+    // split into row ranges so several workers share one batch -- but not finer than ~30 us of decoding: with many
+    // workers the ring holds several batches in flight, and hand-offs, not rows, are what finer tasks multiply
+    const int chunk = std::max(256, (bw->count + cfg_.num_workers - 1) / cfg_.num_workers);
     int ntasks = (bw->count + chunk - 1) / chunk;
     bw->remaining.store(ntasks);
     for (int r = 0; r < bw->count; r += chunk) parse_tasks_.push_back(Task{bw, r, std::min(bw->count, r + chunk), nullptr});
@@ -386,6 +388,7 @@ class Loader {
   }
 
   void reader_main() {
+    pthread_setname_np(pthread_self(), "dfio-batcher");     // names show up in /proc/<pid>/task/*/comm, top -H
     for (int epoch = 0; epoch < cfg_.num_epochs; ++epoch) {
       EpochState es;
       new_batch(es);
@@ -434,6 +437,7 @@ class Loader {
   }
 
   void worker_main() {
+    pthread_setname_np(pthread_self(), "dfio-worker");
     const int F = cfg_.field_size;
     const size_t id_sz = cfg_.ids_i32 ? 4 : 8;
     const uint64_t max_id = cfg_.feature_size > 0 ? static_cast<uint64_t>(cfg_.feature_size) : 0;
@@ -443,7 +447,10 @@ class Loader {
         std::unique_lock<std::mutex> l(mu_);
         cv_task_.wait(l, [&] { return stop_ || failed_ || !parse_tasks_.empty() || !index_tasks_.empty(); });
         if (stop_ || failed_) return;
-        auto& q = !parse_tasks_.empty() ? parse_tasks_ : index_tasks_;     // batches in flight first
+        // Index ranges first: there are at most `window` of them, each ~70 us, and the batcher can build no further
+        // batch until the next range is walked.  Served last, they waited until the parse queue ran dry, and the
+        // workers then idled while the batcher caught up -- a bubble every half dozen batches.
+        auto& q = !index_tasks_.empty() ? index_tasks_ : parse_tasks_;
         t = std::move(q.front());
         q.pop_front();
       }

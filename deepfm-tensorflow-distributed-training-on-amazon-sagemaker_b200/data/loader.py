@@ -116,6 +116,8 @@ class BatchLoader:
             raise DataError(self._lib.dfio_last_error().decode())
         s, n = slot.value, count.value
         self._held = s
+        if n == self.batch_size:     # the common case: the slot's own views, no slicing
+            return HostBatch(self._ids[s], self._vals[s], self._labels[s], n, self._slabs[s], s)
         return HostBatch(self._ids[s][:n], self._vals[s][:n], self._labels[s][:n], n, self._slabs[s], s)
 
     def stats(self):
