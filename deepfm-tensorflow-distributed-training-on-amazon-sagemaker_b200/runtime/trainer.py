@@ -307,7 +307,7 @@ class Trainer:
                     self.train_batch(cur)
                 if deferred:
                     ev = spare.pop() if spare else torch.cuda.Event()
-                    ev.record(torch.cuda.current_stream(self.device))
+                    ev.record(self.engine.current_stream())
                     pending.append((ev, cur.slot))
                 done += 1
                 yield cur
@@ -326,7 +326,7 @@ class Trainer:
         if graph_slot is None:
             self._loss_ring[i].copy_(self.engine.loss_sum_tensor(), non_blocking=True)
         self._loss_src[i] = graph_slot           # None: the trainer's own ring; else: slot of the engine's ring
-        self._loss_ev[i].record(torch.cuda.current_stream(self.device))
+        self._loss_ev[i].record(self.engine.current_stream())
         self._loss_idx ^= 1
         self._issued += 1
         self.global_step += 1
