@@ -294,12 +294,44 @@ class Loader {
         return false;
       }
       expected = std::max(expected, c->stop);
-      for (const RecSpan& r : c->recs) {
-        if (es.idx++ % cfg_.shard_n != cfg_.shard_i) continue;
-        if (!add_record(es, Rec{base + r.off, r.len, seg_of(es, keep, base, 0, path)})) return false;
-      }
+      if (!add_spans(es, c->recs, keep, base, path)) return false;
     }
     bytes_ += static_cast<int64_t>(size);
+    return true;
+  }
+
+  // The records of one indexed range, after the record-level shard, appended to the open batch(es).  This loop is
+  // the batcher thread's whole per-record cost and the one serial stage of the loader, so it is kept to a copy:
+  // no division per record (the shard phase is carried along), the batch's reference to the mapping is looked up
+  // once per run of records, and runs go in with one resize.
+  bool add_spans(EpochState& es, const std::vector<RecSpan>& spans, const std::shared_ptr<const void>& keep,
+                 const uint8_t* base, const std::string& path) {
+    const size_t B = static_cast<size_t>(cfg_.batch_size);
+    const int64_t N = cfg_.shard_n, I = cfg_.shard_i;
+    size_t i = 0;
+    const size_t n = spans.size();
+    while (i < n) {
+      std::vector<Rec>& v = es.bw->recs;
+      const uint32_t seg = seg_of(es, keep, base, 0, path);
+      if (N == 1) {
+        const size_t take = std::min(B - v.size(), n - i);
+        const size_t o = v.size();
+        v.resize(o + take);
+        for (size_t k = 0; k < take; ++k) v[o + k] = Rec{base + spans[i + k].off, spans[i + k].len, seg};
+        i += take;
+        es.idx += static_cast<int64_t>(take);
+      } else {
+        int64_t phase = es.idx % N;
+        for (; i < n && v.size() < B; ++i, ++es.idx) {
+          if (phase == I) v.push_back(Rec{base + spans[i].off, spans[i].len, seg});
+          if (++phase == N) phase = 0;
+        }
+      }
+      if (v.size() == B) {
+        if (!finish_and_submit(es.bw)) return false;
+        new_batch(es);
+      }
+    }
     return true;
   }
 
