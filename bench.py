@@ -149,6 +149,7 @@ def measure_pipeline(trainer, path: str, batch: int, seconds: float = 2.5):
     loss on the host: what `python -m deepfm_b200.train` achieves per rank, input pipeline included."""
     import torch
     from deepfm_b200.data.loader import BatchLoader
+    from deepfm_b200.parallel.sync_dp import chief_decides
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 8)
     workers = max(2, min(32, cores // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
     loader = BatchLoader([path], FIELD, batch, num_epochs=100000, drop_remainder=True, num_workers=workers, num_slots=8,
@@ -165,8 +166,10 @@ def measure_pipeline(trainer, path: str, batch: int, seconds: float = 2.5):
             n += 1
             if n % 64 == 0:
                 loss = trainer.last_loss()
-                if time.time() - t0 >= seconds:
-                    break
+            # every rank must launch the same number of steps (each contains collective kernels that wait for the
+            # peers' same step), so rank 0's clock decides for all -- asked rarely: the broadcast drains the stream
+            if n % 256 == 0 and chief_decides(time.time() - t0 >= seconds, trainer.device):
+                break
     finally:
         cpu1, t1 = thread_cpu_seconds(), time.time()
         gen.close()                              # gives the ring slots back before the loader goes away

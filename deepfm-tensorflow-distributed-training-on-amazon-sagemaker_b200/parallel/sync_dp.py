@@ -88,3 +88,18 @@ def gather_owner_sharded_slots(engine) -> None:
             piece = t[owner::world].contiguous()
             dist.broadcast(piece, src=owner)
             t[owner::world] = piece
+
+
+def chief_decides(flag: bool, device) -> bool:
+    """COLLECTIVE: rank 0's ``flag``, on every rank.
+
+    For any decision that changes how many steps a rank launches -- stop after a time limit, checkpoint now -- taken
+    from a local clock or file system: every step of the fused path contains collective kernels that wait for the same
+    step on every peer, so ranks that decided differently hang until the communication watchdog fires.  Call it at the
+    same step count on all ranks (``train.save_is_due`` and ``bench.measure_pipeline`` do, every N steps); it drains
+    the launching stream, so not every step."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() < 2:
+        return bool(flag)
+    t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=device)
+    dist.broadcast(t, src=0)
+    return bool(t.item())

@@ -233,3 +233,25 @@ def test_owner_sharded_slots_are_gathered_before_a_checkpoint(tmp_path):
         g = torch.load(tmp_path / f"g{r}.pt")
         assert torch.equal(g["w0"], ref) and torch.equal(g["w1"], 2 * ref)
         assert torch.equal(g["v0"], ref[:, None].expand(23, 4)) and torch.equal(g["v1"], 3 * ref[:, None].expand(23, 4))
+
+
+def _decide_worker(rank, world, port, out_dir):
+    from deepfm_b200.parallel.sync_dp import chief_decides
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # the ranks disagree locally in every combination; rank 0's view must win everywhere
+    mine = [(False, True)[(i >> rank) & 1] for i in range(4)]
+    got = [chief_decides(f, torch.device("cpu")) for f in mine]
+    torch.save({"mine": mine, "got": got}, os.path.join(out_dir, f"d{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_stop_and_checkpoint_decisions_are_rank_zeros_on_every_rank(tmp_path):
+    """Ranks that launch different numbers of fused steps hang in the collective kernels: any clock-based decision is
+    rank 0's, broadcast (bench.measure_pipeline, train.save_is_due)."""
+    from deepfm_b200.parallel.sync_dp import chief_decides
+    assert chief_decides(True, torch.device("cpu")) is True and chief_decides(False, torch.device("cpu")) is False
+    mp.spawn(_decide_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    d0, d1 = (torch.load(tmp_path / f"d{i}.pt") for i in range(2))
+    assert d0["mine"] != d1["mine"]
+    assert d0["got"] == d0["mine"] and d1["got"] == d0["mine"]
