@@ -51,6 +51,7 @@ def _feed_fifo(path: str, files: List[str]) -> None:
 
 def _pipe_channels(channels: Dict[str, str], epochs: int, root: str) -> List[threading.Thread]:
     threads = []
+    os.makedirs(root, exist_ok=True)
     for name, src in channels.items():
         files = sorted(glob.glob(os.path.join(src, "**", "*.tfrecords"), recursive=True)) if os.path.isdir(src) else [src]
         for e in range(epochs):

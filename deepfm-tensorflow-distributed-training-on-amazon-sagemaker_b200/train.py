@@ -36,6 +36,7 @@ from .data.sharding import hvd_shard, ps_shard, shard_batches_per_epoch
 from .data.tfrecord import count_records
 from .models.deepfm import DeepFMConfig
 from .parallel.env import DistEnv, detect_env
+from .parallel.even_stream import EvenStream, control_group
 from .runtime.trainer import Trainer, TrainerOptions
 from .utils.checkpoint import CheckpointManager
 from .utils.export import export_servable
@@ -82,10 +83,10 @@ def barrier() -> None:
 
 
 def make_loader(flags: Flags, files: Sequence[str], batch_size: int, shard, drop_remainder: bool,
-                num_epochs: int = 1, streaming: bool = False) -> BatchLoader:
+                num_epochs: int = 1, streaming: bool = False, min_slots: int = 2) -> BatchLoader:
     return BatchLoader(list(files), flags.field_size, batch_size, num_epochs=num_epochs, drop_remainder=drop_remainder,
                        shard_n=shard[0], shard_i=shard[1], num_workers=flags.loader_threads,
-                       num_slots=max(2, flags.prefetch_batches), ids_dtype=torch.int32, verify_crc=True,
+                       num_slots=max(min_slots, flags.prefetch_batches), ids_dtype=torch.int32, verify_crc=True,
                        streaming=streaming, feature_size=flags.feature_size)
 
 
@@ -134,9 +135,13 @@ def save_is_due(trainer: Trainer, ckpt: CheckpointManager, env: DistEnv, every: 
 
 
 def train_epochs(trainer: Trainer, flags: Flags, env: DistEnv, files: Sequence[str], shard, ckpt: CheckpointManager,
-                 num_epochs: int, streaming: bool, max_batches: Optional[int]) -> None:
+                 num_epochs: int, streaming: bool, max_batches: Optional[int], even_group=None) -> None:
+    """``even_group`` (a gloo group over all ranks): the batch count is not known up front (streams), so the ranks
+    agree step by step, two steps ahead, on whether everybody still has a batch (parallel/even_stream.py)."""
     loader = make_loader(flags, files, flags.batch_size, shard, drop_remainder=True, num_epochs=num_epochs,
-                         streaming=streaming)
+                         streaming=streaming, min_slots=6 if even_group is not None else 2)
+    if even_group is not None:
+        loader = EvenStream(loader, even_group, depth=2)
     t0, s0 = time.time(), trainer.global_step
     limit = None if max_batches is None else max_batches * num_epochs
     done = 0
@@ -235,8 +240,11 @@ def main(argv: Optional[List[str]] = None) -> int:
             ch = flags.training_channel_name or (channels[1 + env.local_rank] if len(channels) > 1 + env.local_rank
                                                  else f"training_{env.local_rank}")
             paths = [pipe_channel_path(ch, e) for e in range(flags.num_epochs)]
+            # channels cannot be counted and rarely hold the same number of records: every epoch ends, on every rank,
+            # at the first step some rank has no full batch for (the reference hangs in Horovod there)
+            group = control_group() if env.world_size > 1 else None
             for e, pth in enumerate(paths):
-                train_epochs(trainer, flags, env, [pth], shard, ckpt, 1, True, None)
+                train_epochs(trainer, flags, env, [pth], shard, ckpt, 1, True, None, even_group=group)
             save(trainer, ckpt, env)
             if env.is_chief:
                 log(env, str(run_eval(trainer, flags, [pipe_channel_path(eval_channel, 0)], streaming=True)))

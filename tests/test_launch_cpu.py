@@ -104,6 +104,27 @@ def test_launch_pipe_mode_single_rank(tmp_path, val_tfrecords):
     assert "'auc'" in r.stdout and os.path.exists(tmp_path / "ckpt" / "checkpoint")
 
 
+def test_launch_pipe_mode_two_ranks_with_uneven_channels(tmp_path, val_tfrecords):
+    """NB-HVD pipe mode (256-301): one training channel per local worker (HVD.py:445), and the channels do not hold the
+    same number of records.  The reference hangs in Horovod when one rank runs out; here both ranks stop
+    on the same step and the job finishes: evaluation, checkpoint, export."""
+    recs = list(T.iter_records(val_tfrecords))[:1300]
+    for d, part in (("t0", recs[:600]), ("t1", recs[600:950]), ("val", recs[950:])):
+        (tmp_path / d).mkdir()
+        with T.TFRecordWriter(str(tmp_path / d / ("va_0.tfrecords" if d == "val" else "tr_0.tfrecords"))) as w:
+            for r in part:
+                w.write(r)
+    r = _launch(["--distribution", "mpi", "--processes_per_host", "2", "--input_mode", "Pipe", "--master_port", "29575",
+                 "--pipe_root", str(tmp_path / "pipes"), "--hyperparameters"] + HP +
+                [f"checkpoint_dir={tmp_path / 'ckpt'}", "log_steps=1", "enable_data_multi_path=True",
+                 "--channels", f"training0={tmp_path / 't0'}", f"training1={tmp_path / 't1'}",
+                 f"evaluation={tmp_path / 'val'}"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "current rank is 1 of 2" in r.stdout and "'auc'" in r.stdout
+    assert "step = 3 " in r.stdout and "step = 4 " not in r.stdout        # 350 records = 3 full batches of 100
+    assert os.path.exists(tmp_path / "ckpt" / "checkpoint")
+
+
 def test_launch_parameter_server_two_instances(tmp_path, val_tfrecords):
     """NB-PS in miniature: two 'instances', each with one PS task and one worker task wired by TF_CONFIG."""
     _write_split(tmp_path, val_tfrecords)

@@ -255,3 +255,44 @@ def test_stop_and_checkpoint_decisions_are_rank_zeros_on_every_rank(tmp_path):
     d0, d1 = (torch.load(tmp_path / f"d{i}.pt") for i in range(2))
     assert d0["mine"] != d1["mine"]
     assert d0["got"] == d0["mine"] and d1["got"] == d0["mine"]
+
+
+def _even_worker(rank, world, port, out_dir, counts, batch):
+    from deepfm_b200.parallel.even_stream import EvenStream, control_group
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    path = os.path.join(out_dir, f"ch{rank}.tfrecords")
+    with T.TFRecordWriter(path) as w:
+        for i in range(counts[rank]):
+            w.write_example(float(i & 1), np.arange(8) + (i % 100), np.ones(8, np.float32))
+    group = control_group()
+    cfg = DeepFMConfig(8, 200, 8, [16, 8], [1.0, 1.0], l2_reg=1e-3)
+    tr = Trainer(cfg, TrainerOptions(batch_size=batch, optimizer="GD", learning_rate=0.05, backend="eager", seed=5),
+                 device="cpu")
+    seen = []
+    for epoch in range(2):                       # the wrapper is per epoch, the group is made once
+        loader = EvenStream(BatchLoader([path], 8, batch, streaming=True, num_slots=6, num_workers=2,
+                                        ids_dtype=torch.int32), group, depth=2)
+        n = 0
+        for hb in tr.train_batches(loader):      # every step all-reduces gradients over the ranks: uneven counts would hang
+            assert hb.count == batch
+            n += 1
+        loader.close()
+        seen.append(n)
+    torch.save({"steps": seen, "vars": {k: v.detach().clone() for k, v in tr.variables().items()}},
+               os.path.join(out_dir, f"e{rank}.pt"))
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(240)
+@pytest.mark.parametrize("counts", [(10 * 16, 7 * 16 + 5), (3 * 16, 9 * 16), (16, 0)])
+def test_uneven_streams_end_on_the_same_step_everywhere(tmp_path, counts):
+    """Pipe mode on several ranks: channels of different length.  Every rank must run exactly as many steps as the
+    shortest channel has full batches -- agreed two steps ahead over gloo -- and the replicas must stay identical."""
+    batch = 16
+    mp.spawn(_even_worker, args=(2, _free_port(), str(tmp_path), counts, batch), nprocs=2, join=True)
+    e0, e1 = (torch.load(tmp_path / f"e{i}.pt") for i in range(2))
+    want = min(c // batch for c in counts)
+    assert e0["steps"] == [want, want] and e1["steps"] == [want, want]
+    for k in e0["vars"]:
+        assert torch.equal(e0["vars"][k], e1["vars"][k]), k
