@@ -64,8 +64,12 @@ def latest_export(servable_model_dir: str) -> Optional[str]:
     return os.path.join(servable_model_dir, max(stamps, key=int)) if stamps else None
 
 
-def load_servable(path: str, device: str = "cpu") -> Callable[[np.ndarray, np.ndarray], Dict[str, np.ndarray]]:
-    """``path`` is an export directory or its parent (then the newest export is used)."""
+def load_servable(path: str, device: str = "cpu", backend: str = "eager",
+                  max_batch: int = 4096) -> Callable[[np.ndarray, np.ndarray], Dict[str, np.ndarray]]:
+    """``path`` is an export directory or its parent (then the newest export is used).
+
+    ``backend="fused"`` (CUDA device): requests are answered by the sm_100a inference kernels -- fused embedding gather +
+    FM, tcgen05 MLP layers -- in chunks of at most ``max_batch`` rows, instead of eager PyTorch ops."""
     if not os.path.exists(os.path.join(path, "signature.json")):
         newest = latest_export(path)
         if newest is None:
@@ -78,6 +82,28 @@ def load_servable(path: str, device: str = "cpu") -> Callable[[np.ndarray, np.nd
     model = DeepFM(cfg, seed=0)
     tensors = read_bundle(os.path.join(path, "variables", "variables"))
     model.load_tf_variables({k: torch.from_numpy(v) for k, v in tensors.items()})
+    if backend == "fused":
+        from ..runtime.engine import FusedEngine
+        dev = torch.device(device if str(device).startswith("cuda") else "cuda")
+        engine = FusedEngine(cfg, max_batch, optimizer="GD", device=dev)
+        engine.load_from_module(model)
+
+        def serve_fused(feat_ids, feat_vals) -> Dict[str, np.ndarray]:
+            ids = torch.as_tensor(np.ascontiguousarray(feat_ids, dtype=np.int32)).reshape(-1, cfg.field_size)
+            vals = torch.as_tensor(np.ascontiguousarray(feat_vals, dtype=np.float32)).reshape(-1, cfg.field_size)
+            out = torch.empty(ids.shape[0], dtype=torch.float32)
+            for o in range(0, ids.shape[0], max_batch):
+                i = ids[o:o + max_batch].to(dev).contiguous()
+                v = vals[o:o + max_batch].to(dev).contiguous()
+                out[o:o + i.shape[0]] = engine.forward(i, v).float().cpu()
+            return {"prob": out.numpy()}
+
+        serve_fused.config = cfg
+        serve_fused.model = model
+        serve_fused.engine = engine
+        return serve_fused
+    if backend != "eager":
+        raise ValueError(f"load_servable: unknown backend {backend!r} (eager | fused)")
     model = model.to(device).eval()
 
     def serve(feat_ids, feat_vals) -> Dict[str, np.ndarray]:

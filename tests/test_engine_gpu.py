@@ -494,3 +494,26 @@ def test_partial_batch_between_graph_replays():
     again = tr.last_loss(wait_current=True)
     assert abs(again - full) < 1e-5 * abs(full) + 1e-6
     tr.close()
+
+
+def test_servable_answered_by_the_fused_kernels(tmp_path):
+    """The export of HVD.py:477-493 served through the sm_100a inference kernels (load_servable(backend="fused")):
+    same signature and the same probabilities as the eager loader, request larger than one engine batch."""
+    import numpy as np
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.utils.export import export_servable, load_servable
+    cfg = DeepFMConfig(field_size=39, feature_size=5000, embedding_size=32, deep_layers=[128, 64, 32],
+                       dropout_keep=[0.5] * 3)
+    m = DeepFM(cfg, seed=3)
+    with torch.no_grad():
+        m.fm_v.mul_(30); m.fm_w.mul_(30); m.fm_bias.fill_(-0.2)
+    path = export_servable(m, str(tmp_path / "export"))
+    eager = load_servable(path)
+    fused = load_servable(str(tmp_path / "export"), device="cuda", backend="fused", max_batch=256)
+    rng = np.random.default_rng(0)
+    ids = rng.integers(1, 5000, (700, 39))                  # int64, like the serving signature
+    vals = rng.random((700, 39)).astype(np.float32)
+    a, b = eager(ids, vals)["prob"], fused(ids, vals)["prob"]
+    assert b.shape == (700,) and b.dtype == np.float32
+    assert np.abs(a - b).max() < 1e-2 and a.std() > 0.01
+    fused.engine.close()
