@@ -212,25 +212,32 @@ def test_example_parser_survives_corruption(seed, n_flips, cut):
     assert ids.shape == (39,) and vals.shape == (39,) and np.isfinite(lab) | np.isnan(lab) | np.isinf(lab)
 
 
-@settings(max_examples=25, deadline=None)
+@settings(max_examples=40, deadline=None)
 @given(seed=st.integers(0, 2 ** 31), n=st.integers(1, 300), batch=st.integers(1, 64), workers=st.integers(1, 4),
-       shard_n=st.integers(1, 3))
-def test_loader_delivers_every_record_once_in_order(tmp_path_factory, seed, n, batch, workers, shard_n):
-    """Whatever the batch size, worker count and shard: the loader yields exactly the shard's records, in file order."""
+       shard_n=st.integers(1, 3), n_files=st.integers(1, 4), streaming=st.booleans())
+def test_loader_delivers_every_record_once_in_order(tmp_path_factory, seed, n, batch, workers, shard_n, n_files, streaming):
+    """Whatever the batch size, worker count, shard, number of files (some of them empty, batches span them) and
+    transport (mapped / block stream): the loader yields exactly the shard's records, in file order -- the record index
+    of the shard runs on across files."""
     d = tmp_path_factory.mktemp("prop")
-    path = str(d / "x.tfrecords")
     rng = np.random.default_rng(seed)
     labels = rng.integers(0, 2, n).astype(np.float32)
     first_ids = rng.integers(1, 10 ** 6, n)
-    with T.TFRecordWriter(path) as w:
-        for i in range(n):
-            ids = np.full(5, first_ids[i]); ids[1:] = np.arange(4)
-            w.write(T.encode_example(float(labels[i]), ids, np.ones(5, np.float32), packed=bool(i & 1)))
+    cuts = sorted(int(c) for c in rng.integers(0, n + 1, n_files - 1))
+    bounds = [0] + cuts + [n]
+    paths = []
+    for f in range(n_files):
+        paths.append(str(d / f"x{f}.tfrecords"))
+        with T.TFRecordWriter(paths[-1]) as w:
+            for i in range(bounds[f], bounds[f + 1]):
+                ids = np.full(5, first_ids[i]); ids[1:] = np.arange(4)
+                w.write(T.encode_example(float(labels[i]), ids, np.ones(5, np.float32), packed=bool(i & 1)))
     from deepfm_b200.data.loader import BatchLoader
     for shard_i in range(shard_n):
         got = []
-        loader = BatchLoader([path], 5, batch, num_epochs=1, drop_remainder=False, shard_n=shard_n, shard_i=shard_i,
-                             num_workers=workers, num_slots=3, ids_dtype=torch.int64, pin_memory=False)
+        loader = BatchLoader(paths, 5, batch, num_epochs=1, drop_remainder=False, shard_n=shard_n, shard_i=shard_i,
+                             num_workers=workers, num_slots=3, ids_dtype=torch.int64, pin_memory=False,
+                             streaming=streaming)
         for hb in loader:
             got.extend(zip(hb.feat_ids[:, 0].tolist(), hb.labels.tolist()))
         loader.close()
