@@ -25,6 +25,7 @@
 #include <condition_variable>
 #include <deque>
 #include <mutex>
+#include <new>
 #include <thread>
 
 #include "io_internal.h"
@@ -349,8 +350,8 @@ class Loader {
     if (b->buf.size() < cap) b->buf.resize(cap);
     return std::shared_ptr<StreamBlock>(b.release(), [this](StreamBlock* x) {
       std::lock_guard<std::mutex> l(pool_mu_);
-      if (free_blocks_.size() < 16) free_blocks_.emplace_back(x);
-      else delete x;
+      if (free_blocks_.size() < 16 && x->buf.size() <= 4 * kStreamBlock) free_blocks_.emplace_back(x);
+      else delete x;       // (a block grown for one huge record is not kept around)
     });
   }
 
@@ -372,7 +373,14 @@ class Loader {
           memcpy(&n, blk->buf.data() + pos, 8);
           need = std::max<size_t>(need, n + 16);
         }
-        std::shared_ptr<StreamBlock> nb = get_block(need);
+        std::shared_ptr<StreamBlock> nb;
+        try {
+          nb = get_block(need);
+        } catch (const std::bad_alloc&) {
+          fail(path + ": cannot buffer a record of " + std::to_string(need - 16) + " bytes (stream offset " +
+               std::to_string(blk->stream_off + pos) + ")");
+          return false;
+        }
         memcpy(nb->buf.data(), blk->buf.data() + pos, tail);
         nb->stream_off = blk->stream_off + pos;
         blk = std::move(nb);
