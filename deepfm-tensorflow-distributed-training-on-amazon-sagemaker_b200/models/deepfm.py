@@ -127,7 +127,7 @@ class DeepFM(nn.Module):
         """Returns logits [B]; ``prob = sigmoid(logits)`` (HVD.py:249)."""
         cfg = self.cfg
         feat_ids = feat_ids.long().view(-1, cfg.field_size)
-        feat_vals = feat_vals.float().view(-1, cfg.field_size)
+        feat_vals = feat_vals.to(self._real()).view(-1, cfg.field_size)
         y_w, y_v, e = self.fm_terms(feat_ids, feat_vals)
         return self._tower(y_w, y_v, e, training)
 
@@ -136,7 +136,7 @@ class DeepFM(nn.Module):
         """Same forward, but the table rows are passed in explicitly: ``w_rows[u]``, ``v_rows[u, K]`` are
         the rows of the batch's distinct ids and ``inverse[B, F]`` indexes into them.  Differentiating
         w.r.t. the rows yields the de-duplicated sparse gradient directly."""
-        feat_vals = feat_vals.float().view(-1, self.cfg.field_size)
+        feat_vals = feat_vals.to(self._real()).view(-1, self.cfg.field_size)
         y_w = (F.embedding(inverse, w_rows.unsqueeze(1)).squeeze(-1) * feat_vals).sum(1)
         e = F.embedding(inverse, v_rows) * feat_vals.unsqueeze(-1)
         y_v = 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)
@@ -157,10 +157,15 @@ class DeepFM(nn.Module):
         y_d = (h @ self.out_w).view(-1) + self.out_b
         return self.fm_bias + y_w + y_v + y_d
 
+    def _real(self) -> torch.dtype:
+        """float32, or float64 when the module was converted with ``.double()`` (finite-difference checks)."""
+        return torch.float64 if self.fm_v.dtype == torch.float64 else torch.float32
+
     def data_loss(self, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        labels = labels.to(torch.float64 if logits.dtype == torch.float64 else torch.float32)
         if self.cfg.loss_type == "square_loss":
-            return F.mse_loss(torch.sigmoid(logits), labels.float())
-        return F.binary_cross_entropy_with_logits(logits, labels.float())
+            return F.mse_loss(torch.sigmoid(logits), labels)
+        return F.binary_cross_entropy_with_logits(logits, labels)
 
     def reg_loss(self) -> torch.Tensor:
         l2 = self.cfg.l2_reg

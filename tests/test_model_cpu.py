@@ -174,3 +174,77 @@ def test_exact_auc_torch_matches_numpy_with_ties():
     preds = np.round(rng.random(5000), 2).astype(np.float32)        # many ties
     labels = (rng.random(5000) < 0.3).astype(np.float32)
     assert abs(exact_auc_torch(torch.from_numpy(labels), torch.from_numpy(preds)) - exact_auc(labels, preds)) < 1e-12
+
+
+def test_autograd_gradients_match_finite_differences_in_fp64():
+    """SURVEY 4 (unit - model math): the eager restatement of HVD.py:190-268 is the oracle of every kernel test, so its
+    own gradients are checked once against central differences in double precision (log loss and square loss, with
+    and without batch norm, L2 term included)."""
+    import torch
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    g = torch.Generator().manual_seed(0)
+    ids = torch.randint(0, 30, (6, 4), generator=g)
+    ids[0, 1] = ids[0, 2]                                   # the same row twice in one example
+    vals = torch.rand(6, 4, generator=g, dtype=torch.float64)
+    labels = torch.tensor([1.0, 0.0, 0.0, 1.0, 0.0, 1.0], dtype=torch.float64)
+    for loss_type, bn in (("log_loss", False), ("square_loss", False), ("log_loss", True)):
+        cfg = DeepFMConfig(4, 30, 3, [5, 4], [1.0, 1.0], batch_norm=bn, l2_reg=1e-2, loss_type=loss_type)
+        m = DeepFM(cfg, seed=2).double()
+        with torch.no_grad():
+            m.fm_v.mul_(3); m.fm_w.mul_(3)                  # larger than the init, but no saturated sigmoid
+            for b in m.mlp_b:
+                b.uniform_(0.1, 0.3)                       # keep the ReLUs away from their kink
+        assert m(ids, vals).abs().max() < 6
+        keys = [k for k, _ in m.named_parameters()]
+
+        def f(*ps):
+            state = dict(zip(keys, ps))
+            for k, b in m.named_buffers():                  # training-mode BN moves its averages in place: give it copies
+                state[k] = b.clone()
+            logits = torch.func.functional_call(m, state, (ids, vals), {"training": True})
+            reg = cfg.l2_reg * 0.5 * (state["fm_w"].pow(2).sum() + state["fm_v"].pow(2).sum())
+            return m.data_loss(logits, labels) + reg
+
+        inputs = tuple(p.detach().clone().requires_grad_(True) for _, p in m.named_parameters())
+        assert torch.autograd.gradcheck(f, inputs, eps=1e-6, atol=1e-7, rtol=1e-4), (loss_type, bn)
+
+
+def test_forward_rows_is_forward_with_deduplicated_gradients():
+    """parallel/ps.py trains on the batch's distinct rows: same logits, and the gradient w.r.t. the distinct rows is the
+    scatter-add of the per-position gradients (what IndexedSlices de-duplication gives)."""
+    import torch
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    cfg = DeepFMConfig(6, 50, 4, [8, 4], [1.0, 1.0])
+    m = DeepFM(cfg, seed=1)
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, 12, (16, 6), generator=g)         # few distinct ids: many repeats
+    vals = torch.rand(16, 6, generator=g)
+    labels = (torch.rand(16, generator=g) < 0.5).float()
+    m.data_loss(m(ids, vals), labels).backward()
+    uniq, inverse = ids.unique(return_inverse=True)
+    w_rows = m.fm_w.detach()[uniq].clone().requires_grad_(True)
+    v_rows = m.fm_v.detach()[uniq].clone().requires_grad_(True)
+    logits = m.forward_rows(w_rows, v_rows, inverse, vals)
+    torch.testing.assert_close(logits, m(ids, vals), atol=1e-6, rtol=1e-6)
+    m.data_loss(logits, labels).backward()
+    torch.testing.assert_close(w_rows.grad, m.fm_w.grad[uniq], atol=1e-6, rtol=1e-5)
+    torch.testing.assert_close(v_rows.grad, m.fm_v.grad[uniq], atol=1e-6, rtol=1e-5)
+    untouched = torch.ones(50, dtype=torch.bool); untouched[uniq] = False
+    assert m.fm_v.grad[untouched].abs().max() == 0
+
+
+def test_fm_second_order_identity_equals_the_pairwise_sum():
+    """0.5 * ((sum_f v_f x_f)^2 - sum_f (v_f x_f)^2) summed over K == sum_{f<g} <v_f, v_g> x_f x_g (HVD.py:200-206)."""
+    import torch
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    m = DeepFM(DeepFMConfig(5, 40, 6, [4], [1.0]), seed=4).double()
+    g = torch.Generator().manual_seed(1)
+    ids = torch.randint(0, 40, (7, 5), generator=g)
+    vals = torch.rand(7, 5, generator=g, dtype=torch.float64)
+    _, y_v, _ = m.fm_terms(ids, vals)
+    e = m.fm_v[ids] * vals[..., None]
+    want = torch.zeros(7, dtype=torch.float64)
+    for f in range(5):
+        for h in range(f + 1, 5):
+            want += (e[:, f] * e[:, h]).sum(-1)
+    torch.testing.assert_close(y_v, want, atol=1e-12, rtol=1e-10)
