@@ -413,7 +413,7 @@ def run_ps(flags, env) -> int:
         worker.model.eval()
         auc, loss_sum, n = StreamingAUC(200), 0.0, 0
         loader = BatchLoader(files, cfg.field_size, flags.batch_size, drop_remainder=flags.drop_remainder_eval,
-                             ids_dtype=torch.int64, num_workers=flags.loader_threads, streaming=pipe, feature_size=flags.feature_size)
+                             ids_dtype=torch.int64, num_workers=flags.parser_threads, streaming=pipe, feature_size=flags.feature_size)
         with torch.no_grad():
             for hb in loader:
                 logits = worker.model(hb.feat_ids, hb.feat_vals, training=False)
@@ -439,7 +439,7 @@ def run_ps(flags, env) -> int:
             shard = (n_workers, index)       # several workers on one host: split the stream between them
         loader = BatchLoader(tr, cfg.field_size, flags.batch_size, num_epochs=1 if pipe else flags.num_epochs,
                              drop_remainder=True, shard_n=shard[0], shard_i=shard[1], ids_dtype=torch.int64,
-                             num_workers=flags.loader_threads, streaming=pipe, feature_size=flags.feature_size)
+                             num_workers=flags.parser_threads, streaming=pipe, feature_size=flags.feature_size)
         t_start = t_log = time.time()
         last_eval, steps = t_start, 0
         for hb in loader:
@@ -481,7 +481,7 @@ def run_ps(flags, env) -> int:
             worker.model.eval()
             out_path = os.path.join(flags.val_data_dir or ".", "pred.txt")
             loader = BatchLoader(te, cfg.field_size, flags.batch_size, drop_remainder=flags.drop_remainder_eval,
-                                 ids_dtype=torch.int64, num_workers=flags.loader_threads, streaming=pipe, feature_size=flags.feature_size)
+                                 ids_dtype=torch.int64, num_workers=flags.parser_threads, streaming=pipe, feature_size=flags.feature_size)
             n = 0
             with open(out_path, "w") as fo, torch.no_grad():
                 for hb in loader:

@@ -85,7 +85,7 @@ def barrier() -> None:
 def make_loader(flags: Flags, files: Sequence[str], batch_size: int, shard, drop_remainder: bool,
                 num_epochs: int = 1, streaming: bool = False, min_slots: int = 2) -> BatchLoader:
     return BatchLoader(list(files), flags.field_size, batch_size, num_epochs=num_epochs, drop_remainder=drop_remainder,
-                       shard_n=shard[0], shard_i=shard[1], num_workers=flags.loader_threads,
+                       shard_n=shard[0], shard_i=shard[1], num_workers=flags.parser_threads,
                        num_slots=max(min_slots, flags.prefetch_batches), ids_dtype=torch.int32, verify_crc=True,
                        streaming=streaming, feature_size=flags.feature_size)
 

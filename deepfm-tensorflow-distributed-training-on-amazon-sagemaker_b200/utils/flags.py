@@ -97,8 +97,8 @@ FLAG_SPECS: Dict[str, Tuple[Any, Any, str]] = {
     "drop_remainder_eval": (bool, False, "drop the tail batch in eval/infer like the reference (SURVEY Q4)"),
     "auc_mode": (str, "tf", "{tf, exact, both}: 200-threshold tf.metrics.auc or exact rank AUC"),
     "seed": (int, 0, "RNG seed (init, dropout, file shuffle)"),
-    "loader_threads": (int, 4, "TFRecord parser threads"),
-    "prefetch_batches": (int, 4, "ring depth of pinned batch buffers"),
+    "loader_threads": (int, 0, "TFRecord parser threads (0: the cores this process may use / ranks on this host, 2..16)"),
+    "prefetch_batches": (int, 8, "ring depth of pinned batch buffers"),
     "save_checkpoints_secs": (int, 600, "checkpoint period in seconds (Estimator default)"),
     "keep_checkpoint_max": (int, 5, "checkpoints kept (Estimator default)"),
     "max_steps": (int, 0, "stop after this many optimizer steps (0 = run all epochs)"),
@@ -127,6 +127,15 @@ class Flags:
     @property
     def dropout_keep_list(self) -> List[float]:
         return [float(x) for x in str(self.dropout).split(",") if x.strip()]
+
+    @property
+    def parser_threads(self) -> int:
+        """--loader_threads, or a share of the cores this process may run on (tf.data AUTOTUNE's role, HVD.py:159)."""
+        if int(self.loader_threads) > 0:
+            return int(self.loader_threads)
+        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 4)
+        local = os.environ.get("LOCAL_WORLD_SIZE") or os.environ.get("OMPI_COMM_WORLD_LOCAL_SIZE") or "1"
+        return max(2, min(16, cores // max(1, int(local))))
 
     @property
     def effective_model_dir(self) -> str:
