@@ -1,0 +1,86 @@
+// Host-side fused embedding gather + first-order term + FM second-order interaction, forward and backward
+// (HVD.py:196-206), for the CPU trainers: the parameter-server workers (parallel/ps.py) and the eager back-end on a
+// host without a GPU.  The GPU engine has its own kernels (csrc/cuda/embed_fm.cu); this is the same fusion for the
+// mode the reference runs on CPU instances (1-ps-cpu), where stock PyTorch spends more than half of a step in a
+// dozen element-wise passes over the [B, F, K] embedding block and in embedding_dense_backward.
+//
+// Inputs are the batch's DISTINCT table rows (w_rows[U], v_rows[U, K]) and inverse[B, F] indexing into them, so the
+// backward pass yields the de-duplicated sparse gradient directly.
+//
+//   e[b, f, :] = v_rows[inverse[b, f], :] * x[b, f]
+//   s[b, :]    = sum_f e[b, f, :]
+//   y_v[b]     = 0.5 * sum_k (s[b, k]^2 - sum_f e[b, f, k]^2)          y_w[b] = sum_f w_rows[inverse[b, f]] * x[b, f]
+//
+//   de[b, f, k]                 = g_e[b, f, k] + g_yv[b] * (s[b, k] - e[b, f, k])
+//   g_v_rows[inverse[b, f], k] += de[b, f, k] * x[b, f]                g_w_rows[inverse[b, f]] += g_yw[b] * x[b, f]
+//
+// One pass over the block each way; the K loops vectorise (the hot functions are compiled for AVX2 + FMA as well as
+// for the baseline ISA and picked at load time).
+#include <cstdint>
+#include <cstring>
+
+#if defined(__GNUC__) && defined(__x86_64__)
+#define DFM_CLONES __attribute__((target_clones("arch=haswell", "default")))
+#else
+#define DFM_CLONES
+#endif
+
+extern "C" {
+
+DFM_CLONES
+void dfcpu_embed_fm_fwd(const float* w_rows, const float* v_rows, const int64_t* inverse, const float* x, int64_t B,
+                        int64_t F, int64_t K, float* y_w, float* y_v, float* e, float* s) {
+  for (int64_t b = 0; b < B; ++b) {
+    float* sb = s + b * K;
+    float qsum = 0.f, yw = 0.f;
+    for (int64_t k = 0; k < K; ++k) sb[k] = 0.f;
+    for (int64_t f = 0; f < F; ++f) {
+      const int64_t id = inverse[b * F + f];
+      const float xv = x[b * F + f];
+      const float* row = v_rows + id * K;
+      float* eb = e + (b * F + f) * K;
+      float q = 0.f;
+      for (int64_t k = 0; k < K; ++k) {
+        const float ev = row[k] * xv;
+        eb[k] = ev;
+        sb[k] += ev;
+        q += ev * ev;
+      }
+      qsum += q;
+      yw += w_rows[id] * xv;
+    }
+    float ss = 0.f;
+    for (int64_t k = 0; k < K; ++k) ss += sb[k] * sb[k];
+    y_v[b] = 0.5f * (ss - qsum);
+    y_w[b] = yw;
+  }
+}
+
+// g_w_rows[U] and g_v_rows[U, K] must be zero-filled by the caller; g_yw / g_yv / g_e may be null (no gradient)
+DFM_CLONES
+void dfcpu_embed_fm_bwd(const int64_t* inverse, const float* x, const float* e, const float* s, const float* g_yw,
+                        const float* g_yv, const float* g_e, int64_t B, int64_t F, int64_t K, float* g_w_rows,
+                        float* g_v_rows) {
+  for (int64_t b = 0; b < B; ++b) {
+    const float gw = g_yw ? g_yw[b] : 0.f;
+    const float gv = g_yv ? g_yv[b] : 0.f;
+    const float* sb = s + b * K;
+    for (int64_t f = 0; f < F; ++f) {
+      const int64_t id = inverse[b * F + f];
+      const float xv = x[b * F + f];
+      const float* eb = e + (b * F + f) * K;
+      float* out = g_v_rows + id * K;
+      if (g_e) {
+        const float* ge = g_e + (b * F + f) * K;
+        for (int64_t k = 0; k < K; ++k) out[k] += (ge[k] + gv * (sb[k] - eb[k])) * xv;
+      } else {
+        for (int64_t k = 0; k < K; ++k) out[k] += gv * (sb[k] - eb[k]) * xv;
+      }
+      g_w_rows[id] += gw * xv;
+    }
+  }
+}
+
+int dfcpu_version() { return 1; }
+
+}  // extern "C"

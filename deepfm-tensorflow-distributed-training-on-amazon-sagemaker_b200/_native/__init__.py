@@ -1,8 +1,9 @@
-"""ctypes bindings for the two in-tree native libraries.
+"""ctypes bindings for the in-tree native libraries.
 
 ``cuda()`` returns libdfm_cuda.so (sm_100a kernels, C ABI in include/deepfm_b200.h);
-``io()`` returns libdfm_io.so (host data layer, C ABI in include/deepfm_io.h).
-Both are built by scripts/build_native.py; a missing library is built on first use
+``io()`` returns libdfm_io.so (host data layer, C ABI in include/deepfm_io.h);
+``cpu()`` returns libdfm_cpu.so (host compute ops of the CPU trainers, csrc/cpu/).
+All are built by scripts/build_native.py; a missing library is built on first use
 when a compiler is present, and is otherwise a hard error -- there is no silent
 fallback to another implementation.
 """
@@ -58,6 +59,10 @@ def io() -> ctypes.CDLL:
         lib.dfio_last_error.restype = ctypes.c_char_p
         lib._dfm_typed = True
     return lib
+
+
+def cpu() -> ctypes.CDLL:
+    return _load("libdfm_cpu.so", "cpu")
 
 
 def check(rc: int, what: str = "") -> None:

@@ -137,6 +137,11 @@ class DeepFM(nn.Module):
         the rows of the batch's distinct ids and ``inverse[B, F]`` indexes into them.  Differentiating
         w.r.t. the rows yields the de-duplicated sparse gradient directly."""
         feat_vals = feat_vals.to(self._real()).view(-1, self.cfg.field_size)
+        from ..ops import embed_fm_cpu
+        if embed_fm_cpu.usable(w_rows, v_rows, inverse, feat_vals):
+            # float32 on the host: one fused native pass each way instead of a dozen element-wise ops
+            y_w, y_v, e = embed_fm_cpu.embed_fm(w_rows, v_rows, inverse, feat_vals)
+            return self._tower(y_w, y_v, e, training)
         y_w = (F.embedding(inverse, w_rows.unsqueeze(1)).squeeze(-1) * feat_vals).sum(1)
         e = F.embedding(inverse, v_rows) * feat_vals.unsqueeze(-1)
         y_v = 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)

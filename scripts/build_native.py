@@ -1,8 +1,9 @@
 #!/usr/bin/env python
-"""Builds the two native libraries in-tree.
+"""Builds the native libraries in-tree.
 
   libdfm_cuda.so  csrc/cuda/*.cu   nvcc, sm_100a only (cross-compiles without a GPU)
   libdfm_io.so    csrc/io/*.cc     g++ -O3, host-only data layer
+  libdfm_cpu.so   csrc/cpu/*.cc    g++ -O3, host compute ops of the CPU trainers (AVX2 clones picked at load time)
 
 Objects are rebuilt only when a source or header is newer than the object.
 Outputs land in <package>/_native/ so they travel with the source snapshot.
@@ -87,13 +88,24 @@ def build_io(verbose: bool = False) -> Path:
     return lib
 
 
+def build_cpu(verbose: bool = False) -> Path:
+    srcs = sorted((ROOT / "csrc" / "cpu").glob("*.cc"))
+    OUT.mkdir(parents=True, exist_ok=True)
+    lib = OUT / "libdfm_cpu.so"
+    if srcs and _newer(srcs, lib):
+        _run([CXX, "-O3", "-std=c++17", "-fPIC", "-Wall", "-shared", "-o", str(lib), *map(str, srcs)])
+    return lib
+
+
 def main():
     verbose = "-v" in sys.argv
-    what = [a for a in sys.argv[1:] if not a.startswith("-")] or ["cuda", "io"]
+    what = [a for a in sys.argv[1:] if not a.startswith("-")] or ["cuda", "io", "cpu"]
     if "cuda" in what:
         print("built", build_cuda(verbose))
     if "io" in what:
         print("built", build_io(verbose))
+    if "cpu" in what:
+        print("built", build_cpu(verbose))
 
 
 if __name__ == "__main__":

@@ -248,3 +248,49 @@ def test_fm_second_order_identity_equals_the_pairwise_sum():
         for h in range(f + 1, 5):
             want += (e[:, f] * e[:, h]).sum(-1)
     torch.testing.assert_close(y_v, want, atol=1e-12, rtol=1e-10)
+
+
+@pytest.mark.parametrize("B,F,K,U", [(64, 39, 32, 500), (7, 5, 3, 11), (300, 39, 64, 4000), (1, 1, 16, 1)])
+def test_native_cpu_embed_fm_matches_the_pytorch_expression(B, F, K, U, monkeypatch):
+    """csrc/cpu/embed_fm_cpu.cc (what PS workers and the CPU eager back-end run) against the plain PyTorch expression
+    of HVD.py:196-206: outputs, and gradients w.r.t. the distinct rows with an arbitrary downstream gradient."""
+    import torch
+    from deepfm_b200.models.deepfm import DeepFM, DeepFMConfig
+    from deepfm_b200.ops import embed_fm_cpu
+    g = torch.Generator().manual_seed(B * 7 + K)
+    inverse = torch.randint(0, U, (B, F), generator=g)
+    if F > 1:
+        inverse[0, 1] = inverse[0, 0]                     # a repeated row inside one example
+    vals = torch.rand(B, F, generator=g)
+    w0, v0 = torch.randn(U, generator=g), torch.randn(U, K, generator=g) * 0.3
+    assert embed_fm_cpu.usable(w0, v0, inverse, vals)
+    ge = torch.randn(B, F, K, generator=g)
+    gy = torch.randn(2, B, generator=g)
+
+    def run(native):
+        w, v = w0.clone().requires_grad_(True), v0.clone().requires_grad_(True)
+        if native:
+            y_w, y_v, e = embed_fm_cpu.embed_fm(w, v, inverse, vals)
+        else:
+            y_w = (w[inverse] * vals).sum(1)
+            e = v[inverse] * vals.unsqueeze(-1)
+            y_v = 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)
+        ((y_w * gy[0]).sum() + (y_v * gy[1]).sum() + (e * ge).sum()).backward()
+        return y_w.detach(), y_v.detach(), e.detach(), w.grad, v.grad
+
+    for a, b in zip(run(True), run(False)):
+        torch.testing.assert_close(a, b, atol=2e-5, rtol=1e-4)
+    # only some outputs used downstream: the unused ones arrive as None in backward
+    w, v = w0.clone().requires_grad_(True), v0.clone().requires_grad_(True)
+    embed_fm_cpu.embed_fm(w, v, inverse, vals)[1].sum().backward()
+    e = v0[inverse] * vals.unsqueeze(-1)
+    want = torch.zeros_like(v0).index_add_(0, inverse.reshape(-1), ((e.sum(1, keepdim=True) - e) * vals.unsqueeze(-1)).reshape(-1, K))
+    torch.testing.assert_close(v.grad, want, atol=2e-5, rtol=1e-4)
+    assert w.grad is None or w.grad.abs().max() == 0
+    # the model takes the native path on the host and the switch turns it off
+    m = DeepFM(DeepFMConfig(F, max(U, 2), K, [8], [1.0]), seed=1)
+    rows_w, rows_v = m.fm_w.detach()[:U].clone(), m.fm_v.detach()[:U].clone()
+    a = m.forward_rows(rows_w, rows_v, inverse, vals)
+    monkeypatch.setenv("DFM_CPU_NATIVE", "0")
+    b = m.forward_rows(rows_w, rows_v, inverse, vals)
+    torch.testing.assert_close(a, b, atol=1e-5, rtol=1e-5)
