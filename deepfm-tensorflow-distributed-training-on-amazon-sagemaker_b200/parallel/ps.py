@@ -259,9 +259,14 @@ class PSClient:
 class PSWorker:
     """One model replica.  ``train_batch`` = pull touched state, forward/backward locally, push gradients."""
 
-    def __init__(self, cfg: DeepFMConfig, client: PSClient, seed: int = 0):
+    def __init__(self, cfg: DeepFMConfig, client: PSClient, seed: int = 0, dropout_seed: Optional[int] = None):
+        """``dropout_seed``: key of this worker's dropout stream (default ``seed``; give every worker its own).  The
+        masks come from the counter-based generator the GPU engine uses (utils/philox.py, native on the host): a
+        tenth of the cost of torch's scalar CPU dropout, and reproducible per (seed, local step, layer, row)."""
         self.cfg, self.c = cfg, client
         self.model = DeepFM(cfg, seed=seed)
+        self.dropout_seed = int(seed if dropout_seed is None else dropout_seed)
+        self.local_step = 0
         self.dense_names = [n for n in client.names if n not in TABLES and "moving_" not in n]
         self.stat_names = [n for n in client.names if "moving_" in n]
         self.global_step = 0
@@ -281,6 +286,11 @@ class PSWorker:
 
     def train_batch(self, ids: torch.Tensor, vals: torch.Tensor, labels: torch.Tensor) -> float:
         m = self.model
+        self.local_step += 1
+        if any(k < 1.0 for k in self.cfg.dropout_keep):
+            from ..utils.philox import keep_mask
+            seed, step, keeps = self.dropout_seed, self.local_step, self.cfg.dropout_keep
+            m.dropout_mask_fn = lambda layer, rows, cols: keep_mask(seed, step, layer, rows, cols, keeps[layer])
         self.pull_dense()
         uniq, inverse = ids.long().unique(return_inverse=True)
         w_rows = self.c.pull_rows("fm_w", uniq).requires_grad_(True)
@@ -363,7 +373,7 @@ def run_ps(flags, env) -> int:
         return 0
 
     client = PSClient(cfg, n_ps)
-    worker = PSWorker(cfg, client, seed=flags.seed)
+    worker = PSWorker(cfg, client, seed=flags.seed, dropout_seed=flags.seed * 1000003 + index)
     chief = index == 0
     model_dir = flags.effective_model_dir
     ckpt = CheckpointManager(model_dir if chief else "", flags.keep_checkpoint_max, flags.save_checkpoints_secs)

@@ -294,3 +294,19 @@ def test_native_cpu_embed_fm_matches_the_pytorch_expression(B, F, K, U, monkeypa
     monkeypatch.setenv("DFM_CPU_NATIVE", "0")
     b = m.forward_rows(rows_w, rows_v, inverse, vals)
     torch.testing.assert_close(a, b, atol=1e-5, rtol=1e-5)
+
+
+@pytest.mark.parametrize("rows,cols,keep,layer,step,seed", [(1024, 128, 0.5, 0, 1, 7), (300, 100, 0.9, 2, 12345, 2 ** 40 + 17),
+                                                             (5, 3, 0.3, 1, 2, 0), (17, 64, 1.0, 0, 9, 3)])
+def test_native_keep_mask_is_the_engines_philox_stream(rows, cols, keep, layer, step, seed, monkeypatch):
+    """csrc/cpu dfcpu_keep_mask (what the PS workers draw their dropout from) is bit-equal to the tensor restatement of
+    csrc/cuda/common.cuh dropout_keep_bits8 in utils/philox.py, which the GPU tests compare with the kernels."""
+    from deepfm_b200.utils import philox
+    a = philox.keep_mask(seed, step, layer, rows, cols, keep)
+    monkeypatch.setenv("DFM_CPU_NATIVE", "0")
+    b = philox.keep_mask(seed, step, layer, rows, cols, keep)
+    assert a.dtype == torch.bool and a.shape == (rows, cols) and torch.equal(a, b)
+    if keep < 1.0 and rows * cols > 1000:
+        assert abs(a.float().mean().item() - keep) < 0.02
+    if keep == 1.0:
+        assert bool(a.all())

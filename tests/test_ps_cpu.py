@@ -100,3 +100,41 @@ def test_variable_placement_is_round_robin_per_variable():
     place = P.variable_placement(names, 2)
     assert place["fm_bias"] == 0 and place["fm_w"] == 1 and place["fm_v"] == 0      # fm_v whole on one task
     assert sorted(set(place.values())) == [0, 1]
+
+
+def test_worker_dropout_stream_is_counter_based_and_per_worker():
+    """PS workers draw dropout masks from the engine's Philox stream keyed by (dropout_seed, local step, layer): the same
+    worker replays the same masks, two workers with different keys do not share them."""
+    import torch
+    from deepfm_b200.models.deepfm import DeepFMConfig
+    from deepfm_b200.parallel import ps as P
+
+    class _NoNet(P.PSClient):                      # a client that answers from a local model: no process group needed
+        def __init__(self, cfg):
+            super().__init__(cfg, 1)
+            from deepfm_b200.models.deepfm import DeepFM
+            self.m = DeepFM(cfg, seed=0)
+        def pull_dense_all(self):
+            return {n: t.detach().clone() for n, t in self.m.tf_variables().items() if n not in P.TABLES}
+        def pull_rows(self, name, ids):
+            return self.m.tf_variables()[name].detach()[ids].clone()
+        def push_rows(self, name, ids, grad):
+            self.pushed = getattr(self, "pushed", {}); self.pushed[name] = grad.clone()
+        def push_dense_all(self, values):
+            self.dense = {k: v.detach().clone() for k, v in values.items()}
+        def step_all(self):
+            return 1
+
+    cfg = DeepFMConfig(field_size=6, feature_size=120, embedding_size=4, deep_layers=[16, 8], dropout_keep=[0.5, 0.5])
+    g = torch.Generator().manual_seed(0)
+    ids = torch.randint(1, 120, (32, 6), generator=g)
+    vals, labels = torch.rand(32, 6, generator=g), (torch.rand(32, generator=g) < 0.3).float()
+
+    def grads(dropout_seed):
+        c = _NoNet(cfg)
+        w = P.PSWorker(cfg, c, seed=0, dropout_seed=dropout_seed)
+        w.train_batch(ids, vals, labels)
+        return c.dense["Deep-part/mlp0/weights"]
+
+    a, b, c = grads(11), grads(11), grads(12)
+    assert torch.equal(a, b) and not torch.equal(a, c)
