@@ -44,8 +44,10 @@ class TrainerOptions:
     cuda_graph: bool = True
     scale_lr_by_world: bool = True        # HVD.py:171 (sync-DP); the PS script does not scale (PS.py:180)
     log_steps: int = 0
-    dropout_stream: str = "torch"         # eager back-end: "torch" (its own RNG) | "engine" (the fused engine's Philox
+    dropout_stream: str = "auto"          # eager back-end: "torch" (its own RNG) | "engine" (the fused engine's Philox
                                           # masks for the same seed and step: a rounding-only comparison, utils/philox.py)
+                                          # | "auto": engine on the host, where the native mask generator costs a tenth
+                                          # of torch's scalar dropout; torch on a GPU
 
 
 def _world() -> Tuple[int, int]:
@@ -387,7 +389,7 @@ class Trainer:
     # ---- eager back-end: autograd + restated Horovod collectives ----
     def _eager_step(self, ids: torch.Tensor, vals: torch.Tensor, labels: torch.Tensor) -> None:
         m, opt, cfg = self.model, self.optimizer, self.cfg
-        if self.opts.dropout_stream == "engine":
+        if self.opts.dropout_stream == "engine" or (self.opts.dropout_stream == "auto" and not ids.is_cuda):
             from ..utils.philox import keep_mask
             step, seed, dev = self.global_step + 1, self.opts.seed, ids.device
             m.dropout_mask_fn = lambda layer, rows, cols: keep_mask(seed, step, layer, rows, cols,
