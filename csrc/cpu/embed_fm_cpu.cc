@@ -18,6 +18,8 @@
 // for the baseline ISA and picked at load time).
 #include <cstdint>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #if defined(__GNUC__) && defined(__x86_64__)
 #define DFM_CLONES __attribute__((target_clones("arch=haswell", "default")))
@@ -25,12 +27,13 @@
 #define DFM_CLONES
 #endif
 
-extern "C" {
+namespace {
 
+// rows [b0, b1) of the batch
 DFM_CLONES
-void dfcpu_embed_fm_fwd(const float* w_rows, const float* v_rows, const int64_t* inverse, const float* x, int64_t B,
-                        int64_t F, int64_t K, float* y_w, float* y_v, float* e, float* s) {
-  for (int64_t b = 0; b < B; ++b) {
+void fwd_rows(const float* w_rows, const float* v_rows, const int64_t* inverse, const float* x, int64_t b0, int64_t b1,
+              int64_t F, int64_t K, float* y_w, float* y_v, float* e, float* s) {
+  for (int64_t b = b0; b < b1; ++b) {
     float* sb = s + b * K;
     float qsum = 0.f, yw = 0.f;
     for (int64_t k = 0; k < K; ++k) sb[k] = 0.f;
@@ -56,17 +59,19 @@ void dfcpu_embed_fm_fwd(const float* w_rows, const float* v_rows, const int64_t*
   }
 }
 
-// g_w_rows[U] and g_v_rows[U, K] must be zero-filled by the caller; g_yw / g_yv / g_e may be null (no gradient)
+// the distinct rows [id_lo, id_hi): every thread scans all (b, f) pairs and accumulates only into its own rows, so the
+// scatter-add needs no atomics and the sums are formed in batch order whatever the thread count
 DFM_CLONES
-void dfcpu_embed_fm_bwd(const int64_t* inverse, const float* x, const float* e, const float* s, const float* g_yw,
-                        const float* g_yv, const float* g_e, int64_t B, int64_t F, int64_t K, float* g_w_rows,
-                        float* g_v_rows) {
+void bwd_ids(const int64_t* inverse, const float* x, const float* e, const float* s, const float* g_yw,
+             const float* g_yv, const float* g_e, int64_t B, int64_t F, int64_t K, int64_t id_lo, int64_t id_hi,
+             float* g_w_rows, float* g_v_rows) {
   for (int64_t b = 0; b < B; ++b) {
     const float gw = g_yw ? g_yw[b] : 0.f;
     const float gv = g_yv ? g_yv[b] : 0.f;
     const float* sb = s + b * K;
     for (int64_t f = 0; f < F; ++f) {
       const int64_t id = inverse[b * F + f];
+      if (id < id_lo || id >= id_hi) continue;
       const float xv = x[b * F + f];
       const float* eb = e + (b * F + f) * K;
       float* out = g_v_rows + id * K;
@@ -81,7 +86,49 @@ void dfcpu_embed_fm_bwd(const int64_t* inverse, const float* x, const float* e, 
   }
 }
 
-int dfcpu_version() { return 1; }
+template <typename Fn>
+void parallel_ranges(int64_t n, int threads, int64_t min_per_thread, Fn fn) {
+  int t = threads < 1 ? 1 : threads;
+  if (n / t < min_per_thread) t = static_cast<int>(n / min_per_thread);
+  if (t <= 1) {
+    fn(int64_t(0), n);
+    return;
+  }
+  std::vector<std::thread> pool;
+  const int64_t step = (n + t - 1) / t;
+  for (int i = 1; i < t; ++i) {
+    const int64_t lo = i * step, hi = lo + step < n ? lo + step : n;
+    if (lo < hi) pool.emplace_back([=] { fn(lo, hi); });
+  }
+  fn(int64_t(0), step < n ? step : n);
+  for (auto& th : pool) th.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+// `threads`: how many threads may be used (the caller passes torch.get_num_threads(); small problems stay on one)
+void dfcpu_embed_fm_fwd(const float* w_rows, const float* v_rows, const int64_t* inverse, const float* x, int64_t B,
+                        int64_t F, int64_t K, float* y_w, float* y_v, float* e, float* s, int threads) {
+  parallel_ranges(B, threads < 8 ? threads : 8, 256, [=](int64_t b0, int64_t b1) {
+    fwd_rows(w_rows, v_rows, inverse, x, b0, b1, F, K, y_w, y_v, e, s);
+  });
+}
+
+// g_w_rows[U] and g_v_rows[U, K] must be zero-filled by the caller; g_yw / g_yv / g_e may be null (no gradient)
+void dfcpu_embed_fm_bwd(const int64_t* inverse, const float* x, const float* e, const float* s, const float* g_yw,
+                        const float* g_yv, const float* g_e, int64_t B, int64_t F, int64_t K, int64_t U, float* g_w_rows,
+                        float* g_v_rows, int threads) {
+  // every thread re-reads all (b, f) pairs, so more than a few threads only add scanning (measured: 4.6 / 3.7 / 2.9 ms
+  // with 1 / 2 / 4 threads at B = 2048, slower again with 8)
+  const int t = B * F >= 32768 ? (threads < 4 ? threads : 4) : 1;
+  parallel_ranges(U, t, 64, [=](int64_t lo, int64_t hi) {
+    bwd_ids(inverse, x, e, s, g_yw, g_yv, g_e, B, F, K, lo, hi, g_w_rows, g_v_rows);
+  });
+}
+
+int dfcpu_version() { return 2; }
 
 }  // extern "C"
 

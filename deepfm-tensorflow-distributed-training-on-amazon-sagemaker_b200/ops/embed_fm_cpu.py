@@ -23,9 +23,9 @@ def _get():
     if _lib is None:
         lib = _native.cpu()
         p = C.c_void_p
-        lib.dfcpu_embed_fm_fwd.argtypes = [p, p, p, p, C.c_int64, C.c_int64, C.c_int64, p, p, p, p]
+        lib.dfcpu_embed_fm_fwd.argtypes = [p, p, p, p, C.c_int64, C.c_int64, C.c_int64, p, p, p, p, C.c_int]
         lib.dfcpu_embed_fm_fwd.restype = None
-        lib.dfcpu_embed_fm_bwd.argtypes = [p, p, p, p, p, p, p, C.c_int64, C.c_int64, C.c_int64, p, p]
+        lib.dfcpu_embed_fm_bwd.argtypes = [p, p, p, p, p, p, p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, p, p, C.c_int]
         lib.dfcpu_embed_fm_bwd.restype = None
         _lib = lib
     return _lib
@@ -51,7 +51,7 @@ class _EmbedFm(torch.autograd.Function):
         e = torch.empty(B, F, K, dtype=torch.float32)
         s = torch.empty(B, K, dtype=torch.float32)
         lib.dfcpu_embed_fm_fwd(w_rows.data_ptr(), v_rows.data_ptr(), inverse.data_ptr(), vals.data_ptr(), B, F, K,
-                               y_w.data_ptr(), y_v.data_ptr(), e.data_ptr(), s.data_ptr())
+                               y_w.data_ptr(), y_v.data_ptr(), e.data_ptr(), s.data_ptr(), torch.get_num_threads())
         ctx.save_for_backward(inverse, vals, e, s)
         ctx.rows = v_rows.shape[0]
         ctx.mark_non_differentiable(s)
@@ -67,8 +67,8 @@ class _EmbedFm(torch.autograd.Function):
         g_v = torch.zeros(ctx.rows, K, dtype=torch.float32)
         keep = [t.contiguous() if t is not None else None for t in (g_yw, g_yv, g_e)]     # alive across the call
         lib.dfcpu_embed_fm_bwd(inverse.data_ptr(), vals.data_ptr(), e.data_ptr(), s.data_ptr(),
-                               *[t.data_ptr() if t is not None else None for t in keep], B, F, K,
-                               g_w.data_ptr(), g_v.data_ptr())
+                               *[t.data_ptr() if t is not None else None for t in keep], B, F, K, ctx.rows,
+                               g_w.data_ptr(), g_v.data_ptr(), torch.get_num_threads())
         return g_w, g_v, None, None
 
 

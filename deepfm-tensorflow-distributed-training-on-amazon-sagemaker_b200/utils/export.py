@@ -89,7 +89,11 @@ def load_servable(path: str, device: str = "cpu", backend: str = "eager",
         engine.load_from_module(model)
 
         def serve_fused(feat_ids, feat_vals) -> Dict[str, np.ndarray]:
-            ids = torch.as_tensor(np.ascontiguousarray(feat_ids, dtype=np.int32)).reshape(-1, cfg.field_size)
+            raw = np.asarray(feat_ids)
+            if raw.size and (int(raw.min()) < 0 or int(raw.max()) >= cfg.feature_size):     # before narrowing to int32
+                raise IndexError(f"feat_ids must lie in [0, feature_size = {cfg.feature_size}) "
+                                 "(tf.nn.embedding_lookup raises InvalidArgument there)")
+            ids = torch.as_tensor(np.ascontiguousarray(raw, dtype=np.int32)).reshape(-1, cfg.field_size)
             vals = torch.as_tensor(np.ascontiguousarray(feat_vals, dtype=np.float32)).reshape(-1, cfg.field_size)
             out = torch.empty(ids.shape[0], dtype=torch.float32)
             for o in range(0, ids.shape[0], max_batch):
@@ -110,7 +114,15 @@ def load_servable(path: str, device: str = "cpu", backend: str = "eager",
         with torch.no_grad():
             ids = torch.as_tensor(np.asarray(feat_ids, dtype=np.int64), device=device)
             vals = torch.as_tensor(np.asarray(feat_vals, dtype=np.float32), device=device)
-            return {"prob": torch.sigmoid(model(ids, vals, training=False)).cpu().numpy()}
+            if ids.numel() and (int(ids.min()) < 0 or int(ids.max()) >= cfg.feature_size):
+                raise IndexError(f"feat_ids must lie in [0, feature_size = {cfg.feature_size}) "
+                                 "(tf.nn.embedding_lookup raises InvalidArgument there)")
+            if ids.device.type == "cpu" and ids.dim() == 2:
+                # the whole table as "rows", the ids as the index: float32 on the host takes the fused native gather + FM
+                logits = model.forward_rows(model.fm_w, model.fm_v, ids, vals, training=False)
+            else:
+                logits = model(ids, vals, training=False)
+            return {"prob": torch.sigmoid(logits).cpu().numpy()}
 
     serve.config = cfg
     serve.model = model

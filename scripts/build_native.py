@@ -93,7 +93,7 @@ def build_cpu(verbose: bool = False) -> Path:
     OUT.mkdir(parents=True, exist_ok=True)
     lib = OUT / "libdfm_cpu.so"
     if srcs and _newer(srcs, lib):
-        _run([CXX, "-O3", "-std=c++17", "-fPIC", "-Wall", "-shared", "-o", str(lib), *map(str, srcs)])
+        _run([CXX, "-O3", "-std=c++17", "-fPIC", "-pthread", "-Wall", "-shared", "-o", str(lib), *map(str, srcs)])
     return lib
 
 

@@ -310,3 +310,14 @@ def test_native_keep_mask_is_the_engines_philox_stream(rows, cols, keep, layer, 
         assert abs(a.float().mean().item() - keep) < 0.02
     if keep == 1.0:
         assert bool(a.all())
+
+
+def test_serving_rejects_ids_outside_the_table(tmp_path):
+    from deepfm_b200.utils.export import export_servable, load_servable
+    m = DeepFM(DeepFMConfig(4, 50, 8, [8], [1.0]), seed=1)
+    serve = load_servable(export_servable(m, str(tmp_path / "s")))
+    ok = serve(np.array([[0, 1, 2, 49]]), np.ones((1, 4), np.float32))["prob"]
+    assert ok.shape == (1,)
+    for bad in (50, -1, 2 ** 40):
+        with pytest.raises(IndexError, match="feature_size = 50"):
+            serve(np.array([[0, 1, 2, bad]]), np.ones((1, 4), np.float32))
