@@ -285,14 +285,16 @@ def _even_worker(rank, world, port, out_dir, counts, batch):
 
 
 @pytest.mark.timeout(240)
-@pytest.mark.parametrize("counts", [(10 * 16, 7 * 16 + 5), (3 * 16, 9 * 16), (16, 0)])
+@pytest.mark.parametrize("counts", [(10 * 16, 7 * 16 + 5), (3 * 16, 9 * 16), (16, 0), (6 * 16, 4 * 16 + 15, 5 * 16)])
 def test_uneven_streams_end_on_the_same_step_everywhere(tmp_path, counts):
     """Pipe mode on several ranks: channels of different length.  Every rank must run exactly as many steps as the
     shortest channel has full batches -- agreed two steps ahead over gloo -- and the replicas must stay identical."""
     batch = 16
-    mp.spawn(_even_worker, args=(2, _free_port(), str(tmp_path), counts, batch), nprocs=2, join=True)
-    e0, e1 = (torch.load(tmp_path / f"e{i}.pt") for i in range(2))
+    world = len(counts)
+    mp.spawn(_even_worker, args=(world, _free_port(), str(tmp_path), counts, batch), nprocs=world, join=True)
+    res = [torch.load(tmp_path / f"e{i}.pt") for i in range(world)]
     want = min(c // batch for c in counts)
-    assert e0["steps"] == [want, want] and e1["steps"] == [want, want]
-    for k in e0["vars"]:
-        assert torch.equal(e0["vars"][k], e1["vars"][k]), k
+    for r in res:
+        assert r["steps"] == [want, want]
+        for k in res[0]["vars"]:
+            assert torch.equal(res[0]["vars"][k], r["vars"][k]), k
