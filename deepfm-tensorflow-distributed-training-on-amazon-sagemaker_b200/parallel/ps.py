@@ -77,9 +77,18 @@ class ParameterServer:
     def serve(self) -> None:
         """Single-threaded request loop; ends when every worker has said it is done."""
         hdr = torch.zeros(4, dtype=torch.int64)
+        t_start = t_mark = time.perf_counter()
+        self.idle_s, self.op_s = 0.0, {}
+        last_op = None
         while self.done < self.n_workers:
+            now = time.perf_counter()
+            if last_op is not None:                          # time spent serving the previous request, by kind
+                self.op_s[last_op] = self.op_s.get(last_op, 0.0) + now - t_mark
             src = dist.recv(hdr)
+            t_mark = time.perf_counter()
+            self.idle_s += t_mark - now                      # waiting for a request
             op, vi, n, aux = (int(x) for x in hdr)
+            last_op = op
             name = self.names[vi]
             if op == OP_PULL_ROWS:
                 ids = torch.empty(n, dtype=torch.int64)
@@ -156,6 +165,13 @@ class ParameterServer:
                 dist.send(torch.tensor([self.done], dtype=torch.int64), dst=src)
             else:
                 raise RuntimeError(f"parameter server {self.rank}: unknown request {op} from rank {src}")
+        self.wall_s = time.perf_counter() - t_start
+        if os.environ.get("DFM_PS_STATS"):
+            names = {OP_PULL_ROWS: "pull_rows", OP_PUSH_ROWS: "push_rows", OP_PULL_DENSE: "pull_dense",
+                     OP_PUSH_DENSE: "push_dense", OP_STEP: "step"}
+            busy = {names.get(k, str(k)): round(v, 3) for k, v in sorted(self.op_s.items(), key=lambda kv: -kv[1])}
+            print(f"[ps {self.rank}] wall {self.wall_s:.2f} s, idle {self.idle_s:.2f} s, busy by request {busy}, "
+                  f"variables {list(self.vars)}", flush=True)
 
 
 # =============================================================================== worker side
@@ -234,6 +250,55 @@ class PSClient:
             dist.send(_hdr(OP_PUSH_DENSE), dst=ps)
             dist.send(torch.cat([values[n].detach().reshape(-1).float() for n in names]), dst=ps)
 
+    # -- one training step's traffic, requests first and replies after, so the PS tasks serve it concurrently --------
+    def pull_step(self, uniq: torch.Tensor) -> Tuple[Dict[str, torch.Tensor], torch.Tensor, torch.Tensor]:
+        """(dense variables by name, fm_w rows, fm_v rows) for the distinct ids ``uniq``.  Every request of the step is
+        sent before the first reply is awaited: messages between two processes keep their order, a PS answers its
+        requests in the order they arrive, so the replies come back in the order asked -- and the tasks work at the
+        same time instead of one round trip after another."""
+        uniq = uniq.contiguous()
+        dense_ps = [ps for ps in range(self.n_ps) if self.dense_names_on(ps)]
+        # receives are posted BEFORE anything is sent: a PS blocks in its reply until the worker takes it, and would
+        # then never read the worker's next request (both ends stuck in send)
+        flats, waits = {}, []
+        for ps in dense_ps:
+            names = self.dense_names_on(ps)
+            flats[ps] = torch.empty(sum(int(np.prod(self.shapes[n])) for n in names), dtype=torch.float32)
+        rows = {name: torch.empty((uniq.numel(),) + self.shapes[name][1:], dtype=torch.float32) for name in TABLES}
+        # per PS task the replies arrive in request order: dense first, then the tables in TABLES order
+        for ps in dense_ps:
+            waits.append(dist.irecv(flats[ps], src=ps))
+        for name in TABLES:
+            waits.append(dist.irecv(rows[name], src=self.place[name]))
+        for ps in dense_ps:
+            dist.send(_hdr(OP_PULL_DENSE), dst=ps)
+        for name in TABLES:
+            dist.send(uniq, dst=self._req(name, OP_PULL_ROWS, uniq.numel()))
+        for w in waits:
+            w.wait()
+        out: Dict[str, torch.Tensor] = {}
+        for ps in dense_ps:
+            o = 0
+            for n in self.dense_names_on(ps):
+                k = int(np.prod(self.shapes[n]))
+                out[n] = flats[ps][o:o + k].view(self.shapes[n])
+                o += k
+        return out, rows[TABLES[0]], rows[TABLES[1]]
+
+    def push_step(self, uniq: torch.Tensor, gw: torch.Tensor, gv: torch.Tensor, values: Dict[str, torch.Tensor]) -> int:
+        """Sparse gradients, dense gradients / moving statistics and the end-of-step notice to every PS task, all
+        sent before the step replies are read; returns the global step (kept on task 0)."""
+        self.push_rows("fm_w", uniq, gw)
+        self.push_rows("fm_v", uniq, gv)
+        self.push_dense_all(values)
+        steps = [torch.zeros(1, dtype=torch.int64) for _ in range(self.n_ps)]
+        waits = [dist.irecv(steps[ps], src=ps) for ps in range(self.n_ps)]
+        for ps in range(self.n_ps):
+            dist.send(_hdr(OP_STEP), dst=ps)
+        for w in waits:
+            w.wait()
+        return int(steps[0])
+
     def step_all(self) -> int:
         """Tells every PS task one train_op finished; returns the global step (kept on task 0)."""
         gs = 0
@@ -291,20 +356,22 @@ class PSWorker:
             from ..utils.philox import keep_mask
             seed, step, keeps = self.dropout_seed, self.local_step, self.cfg.dropout_keep
             m.dropout_mask_fn = lambda layer, rows, cols: keep_mask(seed, step, layer, rows, cols, keeps[layer])
-        self.pull_dense()
         uniq, inverse = ids.long().unique(return_inverse=True)
-        w_rows = self.c.pull_rows("fm_w", uniq).requires_grad_(True)
-        v_rows = self.c.pull_rows("fm_v", uniq).requires_grad_(True)
+        dense, w_rows, v_rows = self.c.pull_step(uniq)
         tv = m.tf_variables()
+        with torch.no_grad():
+            for n, t in dense.items():
+                tv[n].copy_(t)
+        w_rows.requires_grad_(True)
+        v_rows.requires_grad_(True)
         for n in self.dense_names:
             tv[n].grad = None
         loss = m.data_loss(m.forward_rows(w_rows, v_rows, inverse, vals, training=True), labels)
         loss.backward()
-        self.c.push_rows("fm_w", uniq, w_rows.grad)
-        self.c.push_rows("fm_v", uniq, v_rows.grad)
         # dense gradients and the BN moving averages (assigned, not optimised) travel as one message per PS task
-        self.c.push_dense_all({**{n: tv[n].grad for n in self.dense_names}, **{n: tv[n] for n in self.stat_names}})
-        self.global_step = self.c.step_all()
+        self.global_step = self.c.push_step(uniq, w_rows.grad, v_rows.grad,
+                                            {**{n: tv[n].grad for n in self.dense_names},
+                                             **{n: tv[n] for n in self.stat_names}})
         self.last_loss = float(loss.detach())
         return self.last_loss
 

@@ -114,15 +114,12 @@ def test_worker_dropout_stream_is_counter_based_and_per_worker():
             super().__init__(cfg, 1)
             from deepfm_b200.models.deepfm import DeepFM
             self.m = DeepFM(cfg, seed=0)
-        def pull_dense_all(self):
-            return {n: t.detach().clone() for n, t in self.m.tf_variables().items() if n not in P.TABLES}
-        def pull_rows(self, name, ids):
-            return self.m.tf_variables()[name].detach()[ids].clone()
-        def push_rows(self, name, ids, grad):
-            self.pushed = getattr(self, "pushed", {}); self.pushed[name] = grad.clone()
-        def push_dense_all(self, values):
+        def pull_step(self, uniq):
+            tv = self.m.tf_variables()
+            dense = {n: t.detach().clone() for n, t in tv.items() if n not in P.TABLES}
+            return dense, tv["fm_w"].detach()[uniq].clone(), tv["fm_v"].detach()[uniq].clone()
+        def push_step(self, uniq, gw, gv, values):
             self.dense = {k: v.detach().clone() for k, v in values.items()}
-        def step_all(self):
             return 1
 
     cfg = DeepFMConfig(field_size=6, feature_size=120, embedding_size=4, deep_layers=[16, 8], dropout_keep=[0.5, 0.5])
