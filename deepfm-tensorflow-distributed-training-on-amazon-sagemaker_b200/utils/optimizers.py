@@ -30,6 +30,32 @@ _SLOT_NAMES = {
 _SLOT_INIT = {"adam": (0.0, 0.0), "adagrad": (1e-8, 0.0), "momentum": (0.0, 0.0), "ftrl": (0.1, 0.0), "gd": (0.0, 0.0)}
 
 
+_cpu_lib = None
+
+
+def _native_adam():
+    """libdfm_cpu's one-pass Adam (csrc/cpu), or None when switched off with DFM_CPU_NATIVE=0."""
+    global _cpu_lib
+    import os
+    if os.environ.get("DFM_CPU_NATIVE", "1") == "0":
+        return None
+    if _cpu_lib is None:
+        import ctypes as C
+        from .. import _native
+        lib = _native.cpu()
+        p, f = C.c_void_p, C.c_float
+        lib.dfcpu_adam_dense.argtypes = [p, p, p, p, C.c_int64, f, f, f, f, C.c_int]
+        lib.dfcpu_adam_dense.restype = None
+        lib.dfcpu_adam_rows.argtypes = [p, p, p, p, p, C.c_int64, C.c_int64, f, f, f, f, C.c_int]
+        lib.dfcpu_adam_rows.restype = None
+        _cpu_lib = lib
+    return _cpu_lib
+
+
+def _host_f32(*ts) -> bool:
+    return all(t is not None and not t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() for t in ts)
+
+
 def canonical_optimizer(name: str) -> str:
     """Accepts the reference's spellings ('Adam', 'Adagrad', 'Momentum', 'ftrl', 'GD') in any case."""
     n = name.strip().lower()
@@ -103,6 +129,13 @@ class TFOptimizer:
     @torch.no_grad()
     def apply_dense(self, var: str, p: torch.Tensor, g: torch.Tensor) -> None:
         s0, s1 = self.ensure_slots(var, p)
+        if self.kind == "adam" and _host_f32(p, s0, s1) and g.shape == p.shape and not g.is_cuda:
+            lib = _native_adam()
+            if lib is not None:
+                g = g.detach().to(torch.float32).contiguous()
+                lib.dfcpu_adam_dense(p.data_ptr(), s0.data_ptr(), s1.data_ptr(), g.data_ptr(), p.numel(),
+                                     self._lr_t(), self.beta1, self.beta2, self.eps, torch.get_num_threads())
+                return
         self._apply(p, g, s0, s1)
 
     @torch.no_grad()
@@ -110,6 +143,17 @@ class TFOptimizer:
         """Lazy sparse update: ``rows`` are distinct indices into dim 0 of ``p``."""
         s0, s1 = self.ensure_slots(var, p)
         rows = rows.long()
+        if self.kind == "adam" and _host_f32(p, s0, s1) and not g_rows.is_cuda and not rows.is_cuda \
+                and g_rows.shape == (rows.numel(),) + tuple(p.shape[1:]):
+            lib = _native_adam()
+            if lib is not None:
+                g = g_rows.detach().to(torch.float32).contiguous()
+                rows = rows.contiguous()
+                K = p[0].numel() if p.dim() > 1 else 1
+                lib.dfcpu_adam_rows(p.data_ptr(), s0.data_ptr(), s1.data_ptr(), rows.data_ptr(), g.data_ptr(),
+                                    rows.numel(), K, self._lr_t(), self.beta1, self.beta2, self.eps,
+                                    torch.get_num_threads())
+                return
         pr = p.index_select(0, rows)
         r0 = s0.index_select(0, rows) if s0 is not None else None
         r1 = s1.index_select(0, rows) if s1 is not None else None

@@ -321,3 +321,31 @@ def test_serving_rejects_ids_outside_the_table(tmp_path):
     for bad in (50, -1, 2 ** 40):
         with pytest.raises(IndexError, match="feature_size = 50"):
             serve(np.array([[0, 1, 2, bad]]), np.ones((1, 4), np.float32))
+
+
+def test_native_adam_matches_the_tensor_formula(monkeypatch):
+    """csrc/cpu dfcpu_adam_dense / dfcpu_adam_rows (what the parameter servers and the CPU trainer apply) against the
+    eager TF formula in TFOptimizer, five steps, dense and lazy-row updates, vector and matrix variables."""
+    g = torch.Generator().manual_seed(0)
+    grads = [torch.randn(300, 32, generator=g) for _ in range(5)]
+    rows = [torch.randperm(300, generator=g)[:40] for _ in range(5)]
+
+    def run():
+        opt = TFOptimizer("Adam", 0.01)
+        w, v, d = torch.ones(300), torch.ones(300, 32), torch.ones(70000)
+        for t in range(5):
+            opt.apply_rows("fm_v", v, rows[t], grads[t][:40])
+            opt.apply_rows("fm_w", w, rows[t], grads[t][:40, 0].contiguous())
+            opt.apply_dense("d", d, grads[t].reshape(-1)[:9600].repeat(8)[:70000].contiguous())
+            opt.finish_step()
+        return w, v, d, opt.slots["fm_v/Adam"], opt.slots["fm_v/Adam_1"], opt.slots["d/Adam_1"]
+
+    native = run()
+    monkeypatch.setenv("DFM_CPU_NATIVE", "0")
+    eager = run()
+    for a, b in zip(native, eager):
+        torch.testing.assert_close(a, b, atol=1e-6, rtol=1e-5)
+    assert not torch.equal(native[1], torch.ones(300, 32))
+    untouched = torch.ones(300, dtype=torch.bool)
+    untouched[torch.cat(rows)] = False
+    assert (native[1][untouched] == 1).all() and (native[3][untouched] == 0).all()
