@@ -92,7 +92,8 @@ def build_cpu(verbose: bool = False) -> Path:
     srcs = sorted((ROOT / "csrc" / "cpu").glob("*.cc"))
     OUT.mkdir(parents=True, exist_ok=True)
     lib = OUT / "libdfm_cpu.so"
-    if srcs and _newer(srcs, lib):
+    hdrs = list((ROOT / "csrc" / "cpu").glob("*.h"))
+    if srcs and _newer(srcs + hdrs, lib):
         _run([CXX, "-O3", "-std=c++17", "-fPIC", "-pthread", "-Wall", "-shared", "-o", str(lib), *map(str, srcs)])
     return lib
 
