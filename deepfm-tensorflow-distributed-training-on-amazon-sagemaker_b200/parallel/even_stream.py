@@ -28,7 +28,13 @@ def control_group():
     """COLLECTIVE: a gloo group over all ranks for host-side agreement (the default group may be NCCL)."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() < 2:
         return None
-    return dist.new_group(backend="gloo")
+    try:
+        return dist.new_group(backend="gloo")
+    except Exception as e:       # noqa: BLE001 -- e.g. a host name gloo cannot resolve: the same on every rank of a box
+        if dist.get_rank() == 0:
+            print(f"[even_stream] no gloo control group ({type(e).__name__}: {e}); channels of unequal length will "
+                  "not be evened out", flush=True)
+        return None
 
 
 class EvenStream:
