@@ -356,7 +356,8 @@ class PSWorker:
             from ..utils.philox import keep_mask
             seed, step, keeps = self.dropout_seed, self.local_step, self.cfg.dropout_keep
             m.dropout_mask_fn = lambda layer, rows, cols: keep_mask(seed, step, layer, rows, cols, keeps[layer])
-        uniq, inverse = ids.long().unique(return_inverse=True)
+        from ..ops.unique_cpu import unique_inverse
+        uniq, inverse = unique_inverse(ids, self.cfg.feature_size)
         dense, w_rows, v_rows = self.c.pull_step(uniq)
         tv = m.tf_variables()
         with torch.no_grad():

@@ -395,7 +395,8 @@ class Trainer:
             m.dropout_mask_fn = lambda layer, rows, cols: keep_mask(seed, step, layer, rows, cols,
                                                                     cfg.dropout_keep[layer], dev)
         ids = ids.long()
-        uniq, inverse = ids.unique(return_inverse=True)
+        from ..ops.unique_cpu import unique_inverse
+        uniq, inverse = unique_inverse(ids, cfg.feature_size)          # torch.unique on a GPU, a table pass on the host
         w_rows = m.fm_w.detach().index_select(0, uniq).requires_grad_(True)
         v_rows = m.fm_v.detach().index_select(0, uniq).requires_grad_(True)
         dense = [(n, p) for n, p in m.trainable_tf_variables().items() if n not in ("fm_w", "fm_v")]

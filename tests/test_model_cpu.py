@@ -349,3 +349,36 @@ def test_native_adam_matches_the_tensor_formula(monkeypatch):
     untouched = torch.ones(300, dtype=torch.bool)
     untouched[torch.cat(rows)] = False
     assert (native[1][untouched] == 1).all() and (native[3][untouched] == 0).all()
+
+
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@settings(max_examples=60, deadline=None)
+@given(seed=st.integers(0, 2 ** 31), rows=st.integers(1, 300), cols=st.integers(1, 40),
+       V=st.sampled_from([7, 5000, 117581, 3_000_000]), skew=st.booleans())
+def test_native_unique_inverse_is_torch_unique(seed, rows, cols, V, skew):
+    """csrc/cpu/unique_cpu.cc (table pass + sort of the distinct ids only; radix sort above 4096 of them) returns exactly
+    what torch.unique(return_inverse=True) returns, and leaves its table clean for the next call."""
+    from deepfm_b200.ops.unique_cpu import unique_inverse
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(0, V, (rows, cols), generator=g)
+    if skew:
+        ids = (ids.double() / V).pow(6).mul(V).long().clamp_(0, V - 1)      # many repeats of small ids
+    for _ in range(2):                                                       # second call: the scratch table was reset
+        u, inv = unique_inverse(ids, V)
+        tu, tinv = ids.unique(return_inverse=True)
+        assert torch.equal(u, tu) and torch.equal(inv, tinv) and inv.shape == ids.shape
+    with pytest.raises(IndexError, match="outside"):
+        bad = ids.clone(); bad[-1, -1] = V
+        unique_inverse(bad, V)
+    u, inv = unique_inverse(ids, V)                                          # still clean after the error path
+    assert torch.equal(u, ids.unique())
+
+
+def test_native_unique_large_batch_uses_the_radix_path():
+    from deepfm_b200.ops.unique_cpu import unique_inverse
+    ids = torch.randint(0, 117581, (2048, 39), generator=torch.Generator().manual_seed(1))
+    u, inv = unique_inverse(ids, 117581)
+    tu, tinv = ids.unique(return_inverse=True)
+    assert u.numel() > 4096 and torch.equal(u, tu) and torch.equal(inv, tinv)
