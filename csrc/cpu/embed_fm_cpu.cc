@@ -22,32 +22,36 @@ using dfcpu::parallel_ranges;
 
 namespace {
 
+constexpr int64_t kMaxK = 512;     // embedding sizes above this take the PyTorch expression (ops/embed_fm_cpu.py)
+
 // rows [b0, b1) of the batch
 DFM_CLONES
 void fwd_rows(const float* w_rows, const float* v_rows, const int64_t* inverse, const float* x, int64_t b0, int64_t b1,
               int64_t F, int64_t K, float* y_w, float* y_v, float* e, float* s) {
   for (int64_t b = b0; b < b1; ++b) {
     float* sb = s + b * K;
-    float qsum = 0.f, yw = 0.f;
+    float yw = 0.f;
+    // sum of squares per component, like s: a scalar running sum would be a loop-carried dependence the compiler may
+    // not reorder, and the whole k loop would stay scalar
+    float qk[kMaxK];
     for (int64_t k = 0; k < K; ++k) sb[k] = 0.f;
+    for (int64_t k = 0; k < K; ++k) qk[k] = 0.f;
     for (int64_t f = 0; f < F; ++f) {
       const int64_t id = inverse[b * F + f];
       const float xv = x[b * F + f];
       const float* row = v_rows + id * K;
       float* eb = e + (b * F + f) * K;
-      float q = 0.f;
       for (int64_t k = 0; k < K; ++k) {
         const float ev = row[k] * xv;
         eb[k] = ev;
         sb[k] += ev;
-        q += ev * ev;
+        qk[k] += ev * ev;
       }
-      qsum += q;
       yw += w_rows[id] * xv;
     }
-    float ss = 0.f;
-    for (int64_t k = 0; k < K; ++k) ss += sb[k] * sb[k];
-    y_v[b] = 0.5f * (ss - qsum);
+    float acc = 0.f;
+    for (int64_t k = 0; k < K; ++k) acc += sb[k] * sb[k] - qk[k];
+    y_v[b] = 0.5f * acc;
     y_w[b] = yw;
   }
 }

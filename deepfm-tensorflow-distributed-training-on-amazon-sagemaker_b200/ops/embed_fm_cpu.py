@@ -36,7 +36,7 @@ def usable(w_rows: torch.Tensor, v_rows: torch.Tensor, inverse: torch.Tensor, va
         return False
     return (not w_rows.is_cuda and not v_rows.is_cuda and not inverse.is_cuda and not vals.is_cuda
             and w_rows.dtype == torch.float32 and v_rows.dtype == torch.float32 and vals.dtype == torch.float32
-            and inverse.dtype == torch.int64 and v_rows.dim() == 2 and inverse.dim() == 2)
+            and inverse.dtype == torch.int64 and v_rows.dim() == 2 and inverse.dim() == 2 and v_rows.shape[1] <= 512)
 
 
 class _EmbedFm(torch.autograd.Function):
